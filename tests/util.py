@@ -1,0 +1,104 @@
+"""Shared helpers for the test-suite (test infrastructure)."""
+import gzip
+import json
+import os
+import random
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+# SURVEY.md 8(a) known-answer table, straight from the reference matcher
+# (n=2, K=2..6, f=0, default algorithm unless stated).  fwd/rc = (motif, copies, start, end).
+KNOWN = [
+    ("GGCATATATATCG", {}, ("AT", 4, 3, 11), ("AT", 4, 2, 10)),
+    ("CGTAAAAAAATGC", {}, ("AA", 3, 4, 10), ("TT", 3, 4, 10)),
+    ("CGTAAAAAAATGC", {"rmhm": True}, None, None),
+    ("CGTANANANATGC", {}, None, None),
+    ("CGTACACNCACACTG", {}, ("CA", 2, 8, 12), ("TG", 2, 3, 7)),
+    ("TTACACGGTGTGAA", {}, ("TG", 2, 8, 12), ("GT", 2, 8, 12)),
+    ("TTACACGGACACAA", {}, ("CA", 2, 9, 13), ("TG", 2, 1, 5)),
+    ("AGAGAGAGAGAGCTTCATGCA", {"f": 5}, ("GA", 3, 5, 11), None),
+    ("CTTCATGCATAGAGAGAGAGAG", {"f": 5}, None, ("TC", 3, 5, 11)),
+    ("TTAGAGAGAGAGAGAGCTTCATGCATTT", {"f": 8}, ("AG", 4, 8, 16), None),
+    ("TTAGAGAGAGAGAGAGCTTCATGCATTT", {"f": 8, "altalgo": False}, None, None),
+    ("ACACACACACACACTTGTGTGGGCAATCAGC", {"f": 9}, ("TG", 3, 15, 21), ("CA", 3, 10, 16)),
+    ("ACACACACACACACTTGTGTGGGCAATCAGC", {"f": 9, "altalgo": False}, None, None),
+    ("CGT....TGC", {}, ("..", 2, 3, 7), ("..", 2, 3, 7)),
+    ("TTACGTAGACGTAGACGTAGACGTT", {}, ("TAGACG", 3, 5, 23), ("TCTACG", 3, 4, 22)),
+    ("TTACGACGACGTT", {"n": 3}, ("ACG", 3, 2, 11), ("CGT", 3, 2, 11)),
+    ("TTACGACGTT", {"n": 3}, None, None),
+    ("TTACACACACACTT", {"ks": [3]}, None, None),
+    ("TTACACACACACTT", {"ks": [4]}, ("CACA", 2, 3, 11), ("TGTG", 2, 3, 11)),
+]
+
+
+def gz_read(name):
+    with gzip.open(os.path.join(GOLDEN, name), "rb") as fh:
+        return fh.read()
+
+
+def manifest():
+    with open(os.path.join(GOLDEN, "MANIFEST.json")) as fh:
+        return json.load(fh)
+
+
+def fuzz_cases():
+    return json.loads(gz_read("fuzz_cases.json.gz"))
+
+
+def edge_cases():
+    with open(os.path.join(GOLDEN, "edge_cases.json")) as fh:
+        return json.load(fh)
+
+
+def flags_to_kwargs(flags):
+    """reference CLI flags -> keyword arguments shared by the oracle and the GPU API."""
+    kw = {"n": 2, "f": 31, "ks": None, "rmhm": False, "altalgo": True, "illumina": False}
+    ks, i = [], 0
+    while i < len(flags):
+        a = flags[i]
+        if a == "-n":
+            kw["n"] = int(flags[i + 1]); i += 1
+        elif a == "-f":
+            kw["f"] = int(flags[i + 1]); i += 1
+        elif a == "-i":
+            kw["illumina"] = True
+        elif a == "-r":
+            kw["rmhm"] = True
+        elif a == "-x":
+            kw["altalgo"] = False
+        elif a[:1] == "-" and a[1:] in "23456":
+            ks.append(int(a[1]))
+        elif a[:2] == "--" and a[3:] == "mer":
+            ks.append(int(a[2]))
+        i += 1
+    kw["ks"] = sorted(set(ks)) or None
+    return kw
+
+
+def synth_fastq(nreads, L, seed, p_str=0.30, p_n=0.02, p_lower=0.01, tag="t", vary_len=False,
+                p_dot=0.0):
+    """Small pure-Python synthetic FASTQ (tests only; the bench uses the C generator)."""
+    rng = random.Random(seed)
+    out = []
+    for idx in range(nreads):
+        ll = L if not vary_len else rng.randint(0, L)
+        s = [rng.choice("ACGT") for _ in range(ll)]
+        if ll and rng.random() < p_str:
+            k = rng.randint(2, 6)
+            motif = [rng.choice("ACGT") for _ in range(k)]
+            c = rng.randint(3, 12)
+            pos = rng.randint(0, max(0, ll - 1))
+            for j in range(k * c):
+                if pos + j < ll:
+                    s[pos + j] = motif[j % k]
+        if ll and rng.random() < p_n:
+            s[rng.randrange(ll)] = "N"
+        if ll and rng.random() < p_dot:
+            s[rng.randrange(ll)] = "."
+        s = "".join(s)
+        if rng.random() < p_lower:
+            s = s.lower()
+        q = "".join(chr(rng.randint(35, 73)) for _ in range(ll))
+        out.append("@%s.%010d/1\n%s\n+\n%s\n" % (tag, idx, s, q))
+    return "".join(out).encode("latin-1")
