@@ -1,0 +1,65 @@
+// host_common.h -- host-side types shared by select_host.cu and stream_host.cu
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "../../include/baitstr_select.h"
+
+namespace bstr {
+
+struct BatchState;
+struct ReadResult;
+struct StreamEngine;
+
+constexpr size_t IN_SLACK = 64;    // readable bytes kept on both sides of a device input batch
+
+// Device (and pinned host) buffers for one in-flight batch.
+struct DeviceSlot {
+    uint8_t *d_in_raw, *d_in;      // d_in = d_in_raw + IN_SLACK
+    uint32_t *d_nlpos, *d_tiles, *d_outlen;
+    ReadResult *d_res;
+    uint8_t *d_out;
+    BatchState *d_state, *h_state;
+    uint8_t *h_out;                // pinned
+    ReadResult *h_res;             // pinned
+    size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres;
+
+    int reserve(struct ::bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need);
+    void release();
+};
+
+}  // namespace bstr
+
+struct bstr_ctx {
+    bstr_params p;
+    int dev;
+    int sm_count;
+    cudaStream_t stream;
+    cudaEvent_t ev[8];
+    bstr::DeviceSlot slot;         // used by bstr_scan_batch / bstr_bench_resident
+    uint8_t *d_seqs; uint64_t *d_off; size_t cap_seqs, cap_off;   // bstr_match_reads
+    uint32_t *d_flush; size_t cap_flush;
+    bstr::StreamEngine *engine;    // bstr_run_files (stream_host.cu)
+    bstr_stats stats;
+    char err[512];
+    bstr_ctx() { memset(this, 0, sizeof(*this)); }
+};
+
+namespace bstr {
+
+void set_error(bstr_ctx *ctx, const char *fmt, ...);
+int cuda_fail(bstr_ctx *ctx, cudaError_t e, const char *what, int line);
+struct ScanParams scan_params(const bstr_ctx *ctx);
+int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
+                    cudaEvent_t *ev);
+int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record);
+void stream_release(bstr_ctx *ctx);
+
+#define CUDA_TRY(call)                                                          \
+    do {                                                                        \
+        cudaError_t e_ = (call);                                                \
+        if (e_ != cudaSuccess) return bstr::cuda_fail(ctx, e_, #call, __LINE__); \
+    } while (0)
+
+}  // namespace bstr

@@ -1,0 +1,214 @@
+// select_host.cu -- host side of libbaitstr_select.so: C ABI (include/baitstr_select.h),
+// device buffers, batch pipeline launches.  The streaming file driver is in stream_host.cu.
+//
+// Host role of the reference that this replaces: Pool/Chunker/pool.map/print loop of
+// /root/reference/src/select_STR_reads.pyx:339-373.  No CPU implementation of the scan
+// exists in this library; every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "host_common.h"
+#include "kernels_v1.cuh"
+
+namespace bstr {
+
+void set_error(bstr_ctx *ctx, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(bstr_ctx *ctx, cudaError_t e, const char *what, int line)
+{
+    set_error(ctx, "CUDA error at %s (select_host.cu:%d): %s", what, line, cudaGetErrorString(e));
+    return BSTR_ERR_CUDA;
+}
+
+static int grow(bstr_ctx *ctx, void **p, size_t *cap, size_t need, bool pinned_host)
+{
+    if (*cap >= need) return BSTR_OK;
+    size_t ncap = need + need / 4 + 4096;
+    if (*p) { if (pinned_host) cudaFreeHost(*p); else cudaFree(*p); *p = nullptr; *cap = 0; }
+    cudaError_t e = pinned_host ? cudaHostAlloc(p, ncap, cudaHostAllocDefault) : cudaMalloc(p, ncap);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, pinned_host ? "cudaHostAlloc" : "cudaMalloc", __LINE__);
+    *cap = ncap;
+    return BSTR_OK;
+}
+
+#define GROW(ptr, cap, need, pinned)                                                     \
+    do { int rc_ = grow(ctx, (void **)&(ptr), &(cap), (need), (pinned)); if (rc_) return rc_; } while (0)
+
+// size every device buffer for a batch of nbytes raw bytes (worst cases)
+int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
+{
+    const uint64_t max_lines = nbytes + 4;                 // every byte a newline
+    const uint64_t max_rec = nbytes / 4 + 2;
+    const uint64_t n_tiles = nbytes / IDX_TILE + 2;
+    GROW(d_in_raw, cap_in, nbytes + 2 * IN_SLACK, false);
+    d_in = d_in_raw + IN_SLACK;
+    GROW(d_nlpos, cap_nlpos, max_lines * 4, false);
+    GROW(d_tiles, cap_tiles, n_tiles * 4, false);
+    GROW(d_res, cap_res, max_rec * sizeof(ReadResult), false);
+    GROW(d_outlen, cap_outlen, max_rec * 4, false);
+    if (out_need < 2 * nbytes + 4096) out_need = 2 * nbytes + 4096;
+    GROW(d_out, cap_out, out_need, false);
+    if (!d_state) {
+        CUDA_TRY(cudaMalloc((void **)&d_state, sizeof(BatchState) + 64));
+        CUDA_TRY(cudaHostAlloc((void **)&h_state, sizeof(BatchState), cudaHostAllocDefault));
+    }
+    return BSTR_OK;
+}
+
+void DeviceSlot::release()
+{
+    cudaFree(d_in_raw); cudaFree(d_nlpos); cudaFree(d_tiles); cudaFree(d_res);
+    cudaFree(d_outlen); cudaFree(d_out); cudaFree(d_state);
+    if (h_state) cudaFreeHost(h_state);
+    if (h_out) cudaFreeHost(h_out);
+    if (h_res) cudaFreeHost(h_res);
+    memset(this, 0, sizeof(*this));
+}
+
+ScanParams scan_params(const bstr_ctx *ctx)
+{
+    ScanParams s;
+    s.n = ctx->p.num_copies < 1 ? 1 : ctx->p.num_copies;
+    s.f = ctx->p.flank < 0 ? 0 : ctx->p.flank;     // a negative flank never rejects anything
+    s.kmask = ctx->p.kmask;
+    s.rmhm = ctx->p.remove_homopolymers != 0;
+    s.altalgo = ctx->p.altalgo != 0;
+    return s;
+}
+
+// Launch the device pipeline for the nbytes at slot.d_in.  Nothing here synchronises.
+int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
+                    cudaEvent_t *ev /* 6 events or NULL */)
+{
+    const ScanParams prm = scan_params(ctx);
+    const unsigned n_tiles = (unsigned)((nbytes + IDX_TILE - 1) / IDX_TILE);
+    unsigned long long *d_total = (unsigned long long *)((uint8_t *)s.d_state + sizeof(BatchState));
+    const int rec_blocks = ctx->sm_count * 8;
+    if (ev) cudaEventRecord(ev[0], st);
+    if (n_tiles) k_count_newlines<<<n_tiles, IDX_THREADS, 0, st>>>(s.d_in, nbytes, s.d_tiles);
+    k_exclusive_scan<<<1, 1024, 0, st>>>(s.d_tiles, n_tiles, d_total);
+    if (n_tiles) k_fill_newlines<<<n_tiles, IDX_THREADS, 0, st>>>(s.d_in, nbytes, s.d_tiles, s.d_nlpos);
+    k_finish_index<<<1, 32, 0, st>>>(s.d_nlpos, d_total, s.d_in, nbytes, final, s.d_state);
+    if (ev) cudaEventRecord(ev[1], st);
+    k_scan_records<<<rec_blocks, 128, 0, st>>>(s.d_in, s.d_nlpos, s.d_state, prm, s.d_res, s.d_outlen);
+    if (ev) cudaEventRecord(ev[2], st);
+    k_scan_outlen<<<1, 1024, 0, st>>>(s.d_outlen, s.d_state);
+    if (ev) cudaEventRecord(ev[3], st);
+    k_format_records<<<rec_blocks, 128, 0, st>>>(s.d_in, s.d_nlpos, s.d_state, s.d_res, s.d_outlen,
+                                                 ctx->p.illumina_quals, s.d_out, s.cap_out);
+    if (ev) cudaEventRecord(ev[4], st);
+    CUDA_TRY(cudaGetLastError());
+    return BSTR_OK;
+}
+
+int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record)
+{
+    if (first_bad == ~0ull) return BSTR_OK;
+    const int code = (int)(first_bad & 0xFF);
+    const long long rec = (long long)(first_bad >> 8);
+    if (bad_record) *bad_record = rec;
+    static const char *msg[] = {"", "header should begin with a @ in a fastq file",
+                                "read should only have ACGTN", "separator line in fastq file should begin with a +",
+                                "file ends inside a record"};
+    set_error(ctx, "malformed FASTQ at record %lld: %s", rec, msg[code <= 4 ? code : 0]);
+    switch (code) {
+        case BAD_HEADER: return BSTR_ERR_FASTQ_HEADER;
+        case BAD_BASES: return BSTR_ERR_FASTQ_BASES;
+        case BAD_SEPARATOR: return BSTR_ERR_FASTQ_SEPARATOR;
+        default: return BSTR_ERR_FASTQ_TRUNCATED;
+    }
+}
+
+}  // namespace bstr
+
+using namespace bstr;
+
+extern "C" {
+
+int bstr_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
+{
+    auto fail = [&](const char *m) -> bstr_ctx * {
+        if (err && errlen) snprintf(err, errlen, "%s", m);
+        return nullptr;
+    };
+    if (!p || p->abi_version != BSTR_ABI_VERSION) return fail("bstr_create: ABI version mismatch");
+    if (p->num_copies < 0) return fail("bstr_create: numcopies must be >= 0");
+    int ndev = bstr_device_count();
+    if (ndev <= 0)
+        return fail("bstr_create: no CUDA device available (this library has no CPU fallback)");
+    bstr_ctx *ctx = new bstr_ctx();
+    ctx->p = *p;
+    if (ctx->p.kmask == 0) ctx->p.kmask = 0x7C;            // 2..6 (select_STR_reads:134-136)
+    ctx->p.kmask &= 0x7C;
+    if (ctx->p.kmask == 0) { delete ctx; return fail("bstr_create: no period in 2..6 selected"); }
+    if (ctx->p.batch_bytes == 0) ctx->p.batch_bytes = 64ull << 20;
+    if (ctx->p.batch_bytes > (2ull << 30)) ctx->p.batch_bytes = 2ull << 30;
+    if (ctx->p.n_devices <= 0) {
+        ctx->p.n_devices = ndev > 16 ? 16 : ndev;
+        for (int i = 0; i < ctx->p.n_devices; i++) ctx->p.devices[i] = i;
+    }
+    for (int i = 0; i < ctx->p.n_devices; i++)
+        if (ctx->p.devices[i] < 0 || ctx->p.devices[i] >= ndev) {
+            delete ctx;
+            return fail("bstr_create: device ordinal out of range");
+        }
+    ctx->dev = ctx->p.devices[0];
+    cudaError_t e = cudaSetDevice(ctx->dev);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    cudaDeviceProp prop;
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, ctx->dev);
+    if (e != cudaSuccess) {
+        if (err && errlen) snprintf(err, errlen, "bstr_create: %s", cudaGetErrorString(e));
+        delete ctx;
+        return nullptr;
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    for (int i = 0; i < 8; i++) cudaEventCreate(&ctx->ev[i]);
+    return ctx;
+}
+
+void bstr_destroy(bstr_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->dev);
+    stream_release(ctx);
+    ctx->slot.release();
+    cudaFree(ctx->d_seqs); cudaFree(ctx->d_off); cudaFree(ctx->d_flush);
+    for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *bstr_last_error(const bstr_ctx *ctx) { return ctx ? ctx->err : "null context"; }
+
+void bstr_get_stats(const bstr_ctx *ctx, bstr_stats *st) { if (ctx && st) *st = ctx->stats; }
+void bstr_reset_stats(bstr_ctx *ctx) { if (ctx) memset(&ctx->stats, 0, sizeof(ctx->stats)); }
+
+void *bstr_host_alloc(size_t nbytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, nbytes ? nbytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void bstr_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+}  // extern "C"
+
+#include "batch_api.inc"

@@ -1,0 +1,145 @@
+/*
+ * baitstr_select.h -- C ABI of libbaitstr_select.so, the B200 (sm_100a) implementation of
+ * BaitSTR's per-read STR detection stage (select_STR_reads).
+ *
+ * This is the drop-in boundary: everything the reference's Python entry point
+ *     select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_quals,
+ *                      check_strs, only_k_mers, remove_homopolymers, debug_flag, altalgo,
+ *                      num_processes, chunksize)        /root/reference/src/select_STR_reads.pyx:339-373
+ * does between "open the FASTQ files" and "print the annotated FASTQ" happens behind
+ * these calls.  Plain C types only; no CUDA, PyTorch or C++ types cross the boundary.
+ * There is no CPU fallback: without a usable CUDA device bstr_create() fails.
+ *
+ * Threading: a context is used by one caller thread at a time.  Buffers returned through
+ * bstr_batch_out belong to the context and stay valid until the next call on it.
+ */
+#ifndef BAITSTR_SELECT_H
+#define BAITSTR_SELECT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSTR_ABI_VERSION 1
+
+/* error codes (negative return values) */
+enum {
+    BSTR_OK = 0,
+    BSTR_ERR_NO_DEVICE = -1,    /* no CUDA device / driver: the product path cannot run      */
+    BSTR_ERR_CUDA = -2,         /* a CUDA call failed; bstr_last_error() has the text        */
+    BSTR_ERR_PARAM = -3,        /* bad argument (e.g. numcopies < 0, no period selected)     */
+    BSTR_ERR_IO = -4,           /* open/read/inflate/write failed                            */
+    BSTR_ERR_FASTQ_HEADER = -10,    /* record does not start with '@'   (fastq.pyx:77)       */
+    BSTR_ERR_FASTQ_BASES = -11,     /* base outside acgtnACGTN.         (fastq.pyx:62-67,81) */
+    BSTR_ERR_FASTQ_SEPARATOR = -12, /* third line does not start '+'    (fastq.pyx:86)       */
+    BSTR_ERR_FASTQ_TRUNCATED = -13, /* file ends inside a record        (fastq.pyx:86)       */
+    BSTR_ERR_TOO_LARGE = -14    /* a single record does not fit the batch buffer             */
+};
+
+/*
+ * Scan parameters = the reference's command-line options
+ * (/root/reference/src/select_STR_reads:74-90,97-123).
+ */
+typedef struct bstr_params {
+    int32_t abi_version;     /* BSTR_ABI_VERSION                                            */
+    int32_t num_copies;      /* -n/--numcopies           default 2                           */
+    int32_t flank;           /* -f/--flanks              default 31                          */
+    int32_t kmask;           /* bit k (2..6) set => -k/--kmer given; 0 => all of 2..6        */
+    int32_t remove_homopolymers; /* -r/--removehm                                           */
+    int32_t altalgo;         /* 1 = default algorithm; 0 = -x/--altalgo given                */
+    int32_t illumina_quals;  /* -i/--illumina: Phred+64 in, Phred+33 out                     */
+    int32_t n_devices;       /* GPUs to use; 0 => all visible                                */
+    int32_t devices[16];     /* CUDA ordinals when n_devices > 0                             */
+    int32_t host_threads;    /* reader/inflate threads hint (from -p); 0 => default          */
+    int32_t want_results;    /* bstr_scan_batch also returns the 16-byte per-read records    */
+    int32_t reserved0;
+    uint64_t batch_bytes;    /* raw FASTQ bytes per device batch; 0 => default (64 MiB)      */
+} bstr_params;
+
+/* 16 bytes per input record, in input order. fck == 0 <=> read not selected.
+ * Coordinates as printed by PrintSequence (select_STR_reads.pyx:174-178): fstart in the
+ * read as given, rstart in the reverse-complemented read. */
+typedef struct bstr_read_result {
+    uint32_t fstart;
+    uint32_t rstart;
+    uint32_t fck;            /* forward copies << 3 | period */
+    uint32_t rck;            /* reverse-complement copies << 3 | period */
+} bstr_read_result;
+
+typedef struct bstr_batch_out {
+    const uint8_t *out;      /* annotated FASTQ of the selected reads, input order           */
+    uint64_t out_bytes;
+    uint64_t consumed;       /* input bytes covered by whole records (== nbytes if final)    */
+    uint64_t n_records;
+    uint64_t n_selected;
+    const bstr_read_result *results;   /* NULL unless params.want_results                    */
+    int64_t bad_record;      /* on a BSTR_ERR_FASTQ_* error: 0-based record index in batch   */
+} bstr_batch_out;
+
+typedef struct bstr_stats {
+    uint64_t records, selected, in_bytes, out_bytes, batches;
+    double h2d_ms, kernel_ms, d2h_ms, wall_ms;     /* summed over batches (CUDA events)      */
+} bstr_stats;
+
+/* result of the device-resident benchmark loop */
+typedef struct bstr_bench_out {
+    double ms_total;         /* CUDA-event time of `steps` passes on the launch stream       */
+    double ms_kernel[8];     /* per-kernel average launch duration, ms                       */
+    char kernel_name[8][32];
+    int32_t n_kernels;
+    int32_t launches_per_step;
+    uint64_t n_records, n_selected, in_bytes, out_bytes;
+    uint64_t out_checksum;   /* FNV-1a of the output bytes of the last pass                  */
+} bstr_bench_out;
+
+typedef struct bstr_ctx bstr_ctx;
+
+/* Create a context on the device(s) named in p.  On failure returns NULL and writes a
+ * message to err (if errlen > 0).  Replaces Pool(num_processes) + pattern compilation
+ * (select_STR_reads.pyx:347-357). */
+bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen);
+void bstr_destroy(bstr_ctx *ctx);
+const char *bstr_last_error(const bstr_ctx *ctx);
+
+/* Whole stage for a list of FASTQ files (".gz" by file-name suffix, fastq.pyx:50), in argv
+ * order, selected reads written to out_fd, "Done processing <path>\n" to err_fd after each
+ * file.  Replaces the file loop of select_STR_reads.pyx:359-370.  Returns BSTR_OK or <0. */
+int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npaths, int out_fd, int err_fd);
+
+/* One batch of raw FASTQ bytes in host memory, starting at a record boundary.  Processes
+ * every record that is complete in the buffer (all of it when `final`, with end-of-file
+ * semantics of fastq.pyx:72-94 for the last line) and returns the formatted output.
+ * H2D copy, kernels and D2H copy are all inside this call. */
+int bstr_scan_batch(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int final,
+                    bstr_batch_out *out);
+
+/* Per-read matcher hook (the GPU counterpart of ProcessSequence / MatchPatternsAndReportBest,
+ * select_STR_reads.pyx:106,294): nreads sequences concatenated in `seqs`, read i occupying
+ * [offsets[i], offsets[i+1]).  Bases may be lower case; they are not validated here. */
+int bstr_match_reads(bstr_ctx *ctx, const uint8_t *seqs, const uint64_t *offsets,
+                     uint64_t nreads, bstr_read_result *results);
+
+/* Upload one batch and run the device pipeline `warmup + steps` times with the input
+ * resident in HBM (no host copies inside the timed region); optionally evict L2 between
+ * passes.  Used by bench.py for the kernel-only throughput and the roofline numbers. */
+int bstr_bench_resident(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int steps,
+                        int warmup, int flush_l2, bstr_bench_out *out);
+
+/* Page-locked host memory for callers that want their batches DMA'd without a staging
+ * copy (bench.py's end-to-end leg).  Plain malloc'd buffers work too, only slower. */
+void *bstr_host_alloc(size_t nbytes);
+void bstr_host_free(void *p);
+
+void bstr_get_stats(const bstr_ctx *ctx, bstr_stats *st);
+void bstr_reset_stats(bstr_ctx *ctx);
+
+/* number of CUDA devices visible (0 if none / no driver) */
+int bstr_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BAITSTR_SELECT_H */
