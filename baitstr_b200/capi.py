@@ -1,0 +1,259 @@
+"""ctypes binding of include/baitstr_select.h (the drop-in C ABI).
+
+Every call goes to libbaitstr_select.so; if the library is missing or there is no CUDA
+device the constructors raise -- there is no fallback path.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ABI_VERSION = 1
+
+
+def library_path():
+    return os.path.join(HERE, "libbaitstr_select.so")
+
+
+class Params(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("num_copies", C.c_int32), ("flank", C.c_int32),
+                ("kmask", C.c_int32), ("remove_homopolymers", C.c_int32), ("altalgo", C.c_int32),
+                ("illumina_quals", C.c_int32), ("n_devices", C.c_int32),
+                ("devices", C.c_int32 * 16), ("host_threads", C.c_int32),
+                ("want_results", C.c_int32), ("reserved0", C.c_int32),
+                ("batch_bytes", C.c_uint64)]
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("out", C.c_void_p), ("out_bytes", C.c_uint64), ("consumed", C.c_uint64),
+                ("n_records", C.c_uint64), ("n_selected", C.c_uint64), ("results", C.c_void_p),
+                ("bad_record", C.c_int64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("records", C.c_uint64), ("selected", C.c_uint64), ("in_bytes", C.c_uint64),
+                ("out_bytes", C.c_uint64), ("batches", C.c_uint64), ("h2d_ms", C.c_double),
+                ("kernel_ms", C.c_double), ("d2h_ms", C.c_double), ("wall_ms", C.c_double)]
+
+
+class BenchOut(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("ms_kernel", C.c_double * 8),
+                ("kernel_name", (C.c_char * 32) * 8), ("n_kernels", C.c_int32),
+                ("launches_per_step", C.c_int32), ("n_records", C.c_uint64),
+                ("n_selected", C.c_uint64), ("in_bytes", C.c_uint64), ("out_bytes", C.c_uint64),
+                ("out_checksum", C.c_uint64)]
+
+
+EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "bstr_scan_batch",
+           "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
+           "bstr_get_stats", "bstr_reset_stats", "bstr_device_count"]
+
+_lib = None
+
+
+class BstrError(RuntimeError):
+    def __init__(self, code, message, bad_record=-1):
+        super().__init__("libbaitstr_select error %d: %s" % (code, message))
+        self.code, self.bad_record = code, bad_record
+
+
+def load_library():
+    """Load libbaitstr_select.so (built in-tree by baitstr_b200/csrc/Makefile)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        raise ImportError("%s is missing: build it with `make -C baitstr_b200/csrc` "
+                          "(there is no CPU fallback)" % path)
+    lib = C.CDLL(path)
+    lib.bstr_create.argtypes = [C.POINTER(Params), C.c_char_p, C.c_size_t]
+    lib.bstr_create.restype = C.c_void_p
+    lib.bstr_destroy.argtypes = [C.c_void_p]
+    lib.bstr_destroy.restype = None
+    lib.bstr_last_error.argtypes = [C.c_void_p]
+    lib.bstr_last_error.restype = C.c_char_p
+    lib.bstr_run_files.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_int]
+    lib.bstr_run_files.restype = C.c_int
+    lib.bstr_scan_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(BatchOut)]
+    lib.bstr_scan_batch.restype = C.c_int
+    lib.bstr_match_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.bstr_match_reads.restype = C.c_int
+    lib.bstr_bench_resident.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
+                                        C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(BenchOut)]
+    lib.bstr_bench_resident.restype = C.c_int
+    lib.bstr_host_alloc.argtypes = [C.c_size_t]
+    lib.bstr_host_alloc.restype = C.c_void_p
+    lib.bstr_host_free.argtypes = [C.c_void_p]
+    lib.bstr_host_free.restype = None
+    lib.bstr_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    lib.bstr_get_stats.restype = None
+    lib.bstr_reset_stats.argtypes = [C.c_void_p]
+    lib.bstr_reset_stats.restype = None
+    lib.bstr_device_count.argtypes = []
+    lib.bstr_device_count.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def device_count():
+    return load_library().bstr_device_count()
+
+
+def kmask_of(ks):
+    m = 0
+    for k in (ks or [2, 3, 4, 5, 6]):
+        k = int(k)
+        if 2 <= k <= 6:
+            m |= 1 << k
+    return m
+
+
+class PinnedBuffer:
+    """Page-locked host memory from bstr_host_alloc, exposed as a numpy uint8 array."""
+
+    def __init__(self, nbytes):
+        self._lib = load_library()
+        self.nbytes = int(nbytes)
+        self.ptr = self._lib.bstr_host_alloc(self.nbytes)
+        if not self.ptr:
+            raise MemoryError("bstr_host_alloc(%d) failed" % nbytes)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr))
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            self._lib.bstr_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """One scan context = the reference's Pool + compiled patterns
+    (/root/reference/src/select_STR_reads.pyx:347-357) for one flag set."""
+
+    def __init__(self, n=2, f=31, ks=None, rmhm=False, altalgo=True, illumina=False,
+                 devices=None, want_results=False, batch_bytes=0, host_threads=0):
+        self._lib = load_library()
+        p = Params()
+        p.abi_version = ABI_VERSION
+        p.num_copies, p.flank, p.kmask = int(n), int(f), kmask_of(ks)
+        p.remove_homopolymers, p.altalgo, p.illumina_quals = int(bool(rmhm)), int(bool(altalgo)), int(bool(illumina))
+        devices = list(devices or [])
+        p.n_devices = len(devices)
+        for i, d in enumerate(devices[:16]):
+            p.devices[i] = int(d)
+        p.host_threads, p.want_results, p.batch_bytes = int(host_threads), int(bool(want_results)), int(batch_bytes)
+        err = C.create_string_buffer(512)
+        self._ctx = self._lib.bstr_create(C.byref(p), err, len(err))
+        if not self._ctx:
+            raise BstrError(-1, err.value.decode("latin-1", "replace"))
+        self.want_results = bool(want_results)
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.bstr_destroy(self._ctx)
+            self._ctx = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _raise(self, rc, bad=-1):
+        raise BstrError(rc, self._lib.bstr_last_error(self._ctx).decode("latin-1", "replace"), bad)
+
+    @staticmethod
+    def _addr(raw):
+        if isinstance(raw, PinnedBuffer):
+            return raw.ptr, raw.nbytes, raw
+        if isinstance(raw, np.ndarray):
+            a = np.ascontiguousarray(raw, dtype=np.uint8)
+            return a.ctypes.data, a.nbytes, a
+        b = bytes(raw)
+        a = np.frombuffer(b, dtype=np.uint8)
+        return (a.ctypes.data if len(b) else None), len(b), a
+
+    def scan_batch(self, raw, final=True, nbytes=None):
+        """raw FASTQ bytes -> (output bytes, info dict).  H2D, kernels and D2H inside."""
+        addr, n, keep = self._addr(raw)
+        if nbytes is not None:
+            n = int(nbytes)
+        bo = BatchOut()
+        rc = self._lib.bstr_scan_batch(self._ctx, addr, n, int(bool(final)), C.byref(bo))
+        if rc:
+            self._raise(rc, bo.bad_record)
+        out = C.string_at(bo.out, bo.out_bytes) if bo.out_bytes else b""
+        info = {"consumed": bo.consumed, "n_records": bo.n_records, "n_selected": bo.n_selected,
+                "out_bytes": bo.out_bytes}
+        if self.want_results:
+            if bo.n_records:
+                arr = np.ctypeslib.as_array((C.c_uint32 * (4 * bo.n_records)).from_address(bo.results))
+                info["results"] = arr.reshape(-1, 4).copy()
+            else:
+                info["results"] = np.zeros((0, 4), dtype=np.uint32)
+        return out, info
+
+    def scan_batch_nocopy(self, raw, final=True, nbytes=None):
+        """Like scan_batch but leaves the output in the library's pinned buffer (bench)."""
+        addr, n, keep = self._addr(raw)
+        if nbytes is not None:
+            n = int(nbytes)
+        bo = BatchOut()
+        rc = self._lib.bstr_scan_batch(self._ctx, addr, n, int(bool(final)), C.byref(bo))
+        if rc:
+            self._raise(rc, bo.bad_record)
+        return bo
+
+    def match_reads(self, seqs):
+        """list of bytes -> uint32 [n, 4] (fstart, rstart, fck, rck); fck = copies << 3 | k."""
+        nreads = len(seqs)
+        off = np.zeros(nreads + 1, dtype=np.uint64)
+        if nreads:
+            off[1:] = np.cumsum([len(s) for s in seqs])
+        blob = np.frombuffer(b"".join(seqs) + b"\0", dtype=np.uint8)
+        res = np.zeros((nreads, 4), dtype=np.uint32)
+        rc = self._lib.bstr_match_reads(self._ctx, blob.ctypes.data, off.ctypes.data, nreads,
+                                        res.ctypes.data)
+        if rc:
+            self._raise(rc)
+        return res
+
+    def run_files(self, paths, out_fd=1, err_fd=2):
+        arr = (C.c_char_p * len(paths))(*[os.fsencode(p) for p in paths])
+        rc = self._lib.bstr_run_files(self._ctx, arr, len(paths), int(out_fd), int(err_fd))
+        if rc:
+            self._raise(rc)
+
+    def bench_resident(self, batches, steps, warmup, flush_l2=False):
+        """batches: list of raw FASTQ buffers (each whole records).  One step = the device
+        pipeline over every batch, inputs resident in HBM."""
+        keep = [self._addr(b) for b in batches]
+        ptrs = (C.c_void_p * len(keep))(*[k[0] for k in keep])
+        sizes = (C.c_uint64 * len(keep))(*[k[1] for k in keep])
+        bo = BenchOut()
+        rc = self._lib.bstr_bench_resident(self._ctx, ptrs, sizes, len(keep), int(steps),
+                                           int(warmup), int(bool(flush_l2)), C.byref(bo))
+        if rc:
+            self._raise(rc)
+        kern = {bo.kernel_name[i].value.decode(): bo.ms_kernel[i] for i in range(bo.n_kernels)}
+        return {"ms_total": bo.ms_total, "kernels_ms": kern, "launches_per_step": bo.launches_per_step,
+                "n_records": bo.n_records, "n_selected": bo.n_selected, "in_bytes": bo.in_bytes,
+                "out_bytes": bo.out_bytes, "out_checksum": bo.out_checksum}
+
+    def stats(self):
+        st = Stats()
+        self._lib.bstr_get_stats(self._ctx, C.byref(st))
+        return {k: getattr(st, k) for k, _ in Stats._fields_}
+
+    def reset_stats(self):
+        self._lib.bstr_reset_stats(self._ctx)

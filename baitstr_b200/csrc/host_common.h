@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
+#include <vector>
 
 #include "../../include/baitstr_select.h"
 
@@ -40,6 +41,7 @@ struct bstr_ctx {
     bstr::DeviceSlot slot;         // used by bstr_scan_batch / bstr_bench_resident
     uint8_t *d_seqs; uint64_t *d_off; size_t cap_seqs, cap_off;   // bstr_match_reads
     uint32_t *d_flush; size_t cap_flush;
+    std::vector<bstr::DeviceSlot> *bench_slots;   // bstr_bench_resident
     bstr::StreamEngine *engine;    // bstr_run_files (stream_host.cu)
     bstr_stats stats;
     char err[512];
@@ -55,6 +57,10 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
                     cudaEvent_t *ev);
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record);
 void stream_release(bstr_ctx *ctx);
+int pipeline_stage_count();
+const char *pipeline_stage_name(int k);
+int pipeline_launches_per_batch();
+constexpr int BSTR_MAX_STAGES = 8;
 
 #define CUDA_TRY(call)                                                          \
     do {                                                                        \

@@ -111,6 +111,14 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
     return BSTR_OK;
 }
 
+int pipeline_stage_count() { return 4; }
+const char *pipeline_stage_name(int k)
+{
+    static const char *names[4] = {"index(newlines)", "k_scan_records", "k_scan_outlen", "k_format_records"};
+    return names[k];
+}
+int pipeline_launches_per_batch() { return 7; }
+
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record)
 {
     if (first_bad == ~0ull) return BSTR_OK;
@@ -180,6 +188,7 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
         return nullptr;
     }
     ctx->sm_count = prop.multiProcessorCount;
+    ctx->bench_slots = new std::vector<DeviceSlot>();
     for (int i = 0; i < 8; i++) cudaEventCreate(&ctx->ev[i]);
     return ctx;
 }
@@ -190,6 +199,7 @@ void bstr_destroy(bstr_ctx *ctx)
     cudaSetDevice(ctx->dev);
     stream_release(ctx);
     ctx->slot.release();
+    if (ctx->bench_slots) { for (auto &s : *ctx->bench_slots) s.release(); delete ctx->bench_slots; }
     cudaFree(ctx->d_seqs); cudaFree(ctx->d_off); cudaFree(ctx->d_flush);
     for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);

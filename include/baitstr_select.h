@@ -87,7 +87,7 @@ typedef struct bstr_stats {
 /* result of the device-resident benchmark loop */
 typedef struct bstr_bench_out {
     double ms_total;         /* CUDA-event time of `steps` passes on the launch stream       */
-    double ms_kernel[8];     /* per-kernel average launch duration, ms                       */
+    double ms_kernel[8];     /* per-stage device time per step (all batches), ms             */
     char kernel_name[8][32];
     int32_t n_kernels;
     int32_t launches_per_step;
@@ -122,11 +122,12 @@ int bstr_scan_batch(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int fina
 int bstr_match_reads(bstr_ctx *ctx, const uint8_t *seqs, const uint64_t *offsets,
                      uint64_t nreads, bstr_read_result *results);
 
-/* Upload one batch and run the device pipeline `warmup + steps` times with the input
- * resident in HBM (no host copies inside the timed region); optionally evict L2 between
- * passes.  Used by bench.py for the kernel-only throughput and the roofline numbers. */
-int bstr_bench_resident(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int steps,
-                        int warmup, int flush_l2, bstr_bench_out *out);
+/* Upload `nbatches` batches (each a whole number of records, as bstr_scan_batch with
+ * final = 1) and run the device pipeline over all of them `warmup + steps` times with the
+ * input resident in HBM (no host copies inside the timed region); optionally evict L2
+ * between passes.  Used by bench.py for the kernel-only throughput and the roofline. */
+int bstr_bench_resident(bstr_ctx *ctx, const uint8_t *const *raws, const uint64_t *nbytes,
+                        int nbatches, int steps, int warmup, int flush_l2, bstr_bench_out *out);
 
 /* Page-locked host memory for callers that want their batches DMA'd without a staging
  * copy (bench.py's end-to-end leg).  Plain malloc'd buffers work too, only slower. */

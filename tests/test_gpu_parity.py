@@ -1,0 +1,269 @@
+"""GPU parity tests: the CUDA path (through the C ABI, libbaitstr_select.so) against the
+oracle (oracle/str_oracle.c, pinned to the unmodified reference) and against the golden
+fixtures generated from the reference itself.  Bar: byte-identical output."""
+import gzip
+import hashlib
+import os
+import random
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from baitstr_b200 import capi as m
+    assert m.device_count() > 0, "no CUDA device: the product path cannot run (no fallback)"
+    return m
+
+
+def expect4(seq, **kw):
+    s = seq.upper()
+    fwd = oracle.match_strand(s, **kw)
+    if fwd is None:
+        return (0, 0, 0, 0)
+    rc = oracle.match_strand(oracle.revcomp(s), **kw)
+    fck = fwd[1] << 3 | len(fwd[0])
+    if rc is None:
+        return (fwd[2], 0, fck, 0)
+    return (fwd[2], rc[2], fck, rc[1] << 3 | len(rc[0]))
+
+
+def test_known_answers(capi):
+    for seq, kw, fwd, rc in util.KNOWN:
+        args = dict(n=kw.get("n", 2), f=kw.get("f", 0), ks=kw.get("ks"),
+                    rmhm=kw.get("rmhm", False), altalgo=kw.get("altalgo", True))
+        with capi.Context(**args) as ctx:
+            got = tuple(int(x) for x in ctx.match_reads([seq.encode()])[0])
+        assert got == expect4(seq, **args), (seq, kw)
+        if fwd is not None:
+            assert got[0] == fwd[2] and got[2] == (fwd[1] << 3 | len(fwd[0]))
+        else:
+            assert got[2] == 0
+
+
+def test_reference_fuzz_goldens(capi):
+    """6000+ strings whose answers came from the unmodified reference matcher."""
+    by = {}
+    for c in util.fuzz_cases():
+        by.setdefault((c["n"], c["f"], tuple(c["ks"]), c["rmhm"], c["alt"]), []).append(c)
+    for (n, f, ks, rmhm, alt), cs in by.items():
+        with capi.Context(n=n, f=f, ks=list(ks), rmhm=rmhm, altalgo=alt) as ctx:
+            got = ctx.match_reads([c["s"].encode("latin-1") for c in cs])
+        for c, g in zip(cs, got):
+            fwd, rc = c["fwd"], c["rc"]
+            if fwd is None:
+                want = (0, 0, 0, 0)
+            elif rc is None:
+                want = (fwd[2], 0, fwd[1] << 3 | len(fwd[0]), 0)
+            else:
+                want = (fwd[2], rc[2], fwd[1] << 3 | len(fwd[0]), rc[1] << 3 | len(rc[0]))
+            assert tuple(int(x) for x in g) == want, c
+
+
+@pytest.mark.parametrize("tag", ["default", "readme", "n3r", "k23f41", "x"])
+def test_testdata_goldens(capi, tag):
+    """BASELINE config C1: the shipped test_data, byte-identical to the reference's output."""
+    man = util.manifest()["testdata_" + tag]
+    kw = util.flags_to_kwargs(man["flags"])
+    with capi.Context(**kw) as ctx:
+        out = b"".join(ctx.scan_batch(util.gz_read("testdata_%d.fq.gz" % i))[0] for i in (1, 2))
+    assert hashlib.md5(out).hexdigest() == man["md5"]
+    assert out == util.gz_read("testdata_%s.out.gz" % tag)
+
+
+def test_parser_edge_cases(capi):
+    for name, case in util.edge_cases().items():
+        raw = case["input"].encode("latin-1")
+        with capi.Context(n=2, f=3) as ctx:
+            if name == "high_bytes_qual":
+                # the Py3 shim of the reference cannot carry bytes > 127; the oracle and the
+                # GPU path are 8-bit clean and must agree with each other
+                assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, n=2, f=3)
+            elif case["ok"]:
+                assert ctx.scan_batch(raw)[0] == case["stdout"].encode("latin-1"), name
+            else:
+                with pytest.raises(capi.BstrError) as ei:
+                    ctx.scan_batch(raw)
+                assert ei.value.code <= -10, name
+                with pytest.raises(oracle.OracleError) as oi:
+                    oracle.select_buffer(raw, n=2, f=3)
+                assert ei.value.bad_record == oi.value.record, name
+
+
+ERRMAP = {-1: -10, -2: -11, -3: -12, -4: -13}     # oracle code -> BSTR_ERR_FASTQ_*
+
+FLAGSETS = [
+    dict(),                                             # C2 / C5 flags
+    dict(n=3, rmhm=True),                               # C3
+    dict(ks=[2, 3], f=41),                              # C4
+    dict(n=3, f=29, illumina=True),                     # README pipeline flags
+    dict(altalgo=False, f=10),
+    dict(altalgo=False, rmhm=True, f=5, n=3),
+    dict(n=1, f=0), dict(n=5, f=6, ks=[4, 6]), dict(n=2, f=7, ks=[5], rmhm=True),
+]
+
+
+@pytest.mark.parametrize("fi", range(len(FLAGSETS)))
+def test_synthetic_fastq_vs_oracle(capi, fi):
+    kw = FLAGSETS[fi]
+    with capi.Context(want_results=True, **kw) as ctx:
+        for L, vary, p_dot in [(100, False, 0.0), (150, False, 0.05), (250, False, 0.0),
+                               (120, True, 0.1), (33, True, 0.0), (700, True, 0.02)]:
+            raw = util.synth_fastq(3000, L, seed=fi * 100 + L, p_str=0.6, p_n=0.1, p_lower=0.05,
+                                   vary_len=vary, p_dot=p_dot)
+            want, wres = oracle.select_buffer(raw, want_results=True, **kw)
+            got, info = ctx.scan_batch(raw)
+            assert info["n_records"] == 3000 and info["consumed"] == len(raw)
+            assert info["n_selected"] == int(wres[:, 0].sum())
+            res = info["results"]
+            sel = wres[:, 0] == 1
+            assert np.array_equal(res[:, 2] != 0, sel)
+            assert np.array_equal(res[sel, 0], wres[sel, 3].astype(np.uint32))
+            assert np.array_equal(res[sel, 1], wres[sel, 6].astype(np.uint32))
+            assert np.array_equal(res[sel, 2], (wres[sel, 2] << 3 | wres[sel, 1]).astype(np.uint32))
+            assert np.array_equal(res[sel, 3], (wres[sel, 5] << 3 | wres[sel, 4]).astype(np.uint32))
+            assert got == want, (kw, L)
+
+
+def test_adversarial_reads_vs_oracle(capi):
+    """Repeats straddling the flank boundaries, homopolymers, N / '.' inside repeats, ties
+    between motifs and starts, low-complexity alphabets (the cases SURVEY.md 8a warns about)."""
+    rng = random.Random(20261104)
+    for it in range(40):
+        n = rng.choice([1, 2, 2, 3, 4]); f = rng.choice([0, 3, 6, 7, 10, 31, 41])
+        ks = rng.choice([None, [2], [3], [6], [2, 3], [4, 5], [2, 6], [3, 4, 5, 6]])
+        rmhm, alt = rng.random() < 0.4, rng.random() < 0.75
+        alpha = rng.choice(["ACGT", "AC", "ACGTN", "ACGT.", "A", "AT"])
+        seqs = []
+        for _ in range(400):
+            L = rng.choice([0, 1, 5, 31, 32, 33, 63, 64, 65, 76, 100, 101, 127, 128, 129, 150, 200,
+                            250, 255, 256, 257, 300, 511, 512, 600, 1500])
+            s = [rng.choice(alpha) for _ in range(L)]
+            for _ in range(rng.choice([0, 1, 1, 2, 3])):
+                k = rng.randint(1, 6); m = [rng.choice(alpha) for _ in range(k)]
+                c = rng.randint(2, 14); p = rng.randint(0, max(0, L - 1))
+                for j in range(k * c):
+                    if p + j < L:
+                        s[p + j] = m[j % k]
+            if L and rng.random() < 0.2:
+                s[rng.randrange(L)] = rng.choice("N.")
+            s = "".join(s)
+            seqs.append(s.lower() if rng.random() < 0.1 else s)
+        kw = dict(n=n, f=f, ks=ks, rmhm=rmhm, altalgo=alt)
+        with capi.Context(**kw) as ctx:
+            got = ctx.match_reads([s.encode() for s in seqs])
+        for s, g in zip(seqs, got):
+            assert tuple(int(x) for x in g) == expect4(s, **kw), (s, kw)
+
+
+def test_batch_boundaries_and_errors(capi):
+    raw = util.synth_fastq(500, 100, seed=5)
+    want = oracle.select_buffer(raw)
+    with capi.Context() as ctx:
+        # non-final batches: only whole records are consumed, the tail is carried
+        out, pos = [], 0
+        for cut in (1, 17, 223, 224, 5000, 40001, len(raw)):
+            chunk = raw[pos:cut]
+            final = cut == len(raw)
+            o, info = ctx.scan_batch(chunk, final=final)
+            out.append(o)
+            assert info["consumed"] <= len(chunk)
+            pos += info["consumed"]
+            if not final:
+                assert info["consumed"] == 0 or chunk[info["consumed"] - 1:info["consumed"]] == b"\n"
+        assert pos == len(raw) and b"".join(out) == want
+        # the first bad record is reported with the reference's error class
+        for bad_at, mut in [(7, lambda r: r.replace(b"@", b"X", 1)), (123, lambda r: r.replace(b"\n+\n", b"\n-\n", 1))]:
+            recs = raw.split(b"\n")
+            lines = [recs[i * 4:(i + 1) * 4] for i in range(500)]
+            lines[bad_at] = mut(b"\n".join(lines[bad_at])).split(b"\n")
+            bad = b"\n".join(b"\n".join(x) for x in lines) + b"\n"
+            with pytest.raises(capi.BstrError) as ei:
+                ctx.scan_batch(bad)
+            with pytest.raises(oracle.OracleError) as oi:
+                oracle.select_buffer(bad)
+            assert ei.value.bad_record == oi.value.record == bad_at
+            assert ei.value.code == ERRMAP[oi.value.code]
+        # the context is still usable after an error
+        assert ctx.scan_batch(raw)[0] == want
+
+
+def test_run_files_plain_gz_and_small_batches(capi, tmp_path):
+    """bstr_run_files: argv order, '.gz' by suffix, 'Done processing' lines, batch carry-over."""
+    r1 = util.synth_fastq(4000, 100, seed=11, tag="a")
+    r2 = util.synth_fastq(3000, 150, seed=12, tag="b", vary_len=True)
+    p1, p2 = str(tmp_path / "r1.fq"), str(tmp_path / "r2.fq.gz")
+    open(p1, "wb").write(r1)
+    with gzip.open(p2, "wb") as fh:
+        fh.write(r2)
+    want = oracle.select_buffer(r1) + oracle.select_buffer(r2)
+    for bb in (0, 64 << 10, 1 << 20):
+        outp, errp = str(tmp_path / "out.fq"), str(tmp_path / "err.txt")
+        with capi.Context(batch_bytes=bb) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            ctx.run_files([p1, p2], out_fd=fo.fileno(), err_fd=fe.fileno())
+            st = ctx.stats()
+        assert open(outp, "rb").read() == want, bb
+        assert open(errp).read() == "Done processing %s\nDone processing %s\n" % (p1, p2)
+        assert st["records"] == 7000
+
+
+def test_cli_end_to_end(capi, tmp_path):
+    """The drop-in CLI on the shipped test data with the README flags (-i -n 3 -f 29)."""
+    paths = []
+    for i in (1, 2):
+        p = str(tmp_path / ("Illumina_100_500_%d.fq" % i))
+        open(p, "wb").write(util.gz_read("testdata_%d.fq.gz" % i))
+        paths.append(p)
+    cli = os.path.join(util.ROOT, "bin", "select_STR_reads")
+    for tag in ("readme", "default", "k23f41"):
+        man = util.manifest()["testdata_" + tag]
+        r = subprocess.run([sys.executable, cli] + man["flags"] + ["-p", "4", "-s", "100"] + paths,
+                           capture_output=True)
+        assert r.returncode == 0, r.stderr
+        assert hashlib.md5(r.stdout).hexdigest() == man["md5"]
+        assert r.stderr.decode() == "".join("Done processing %s\n" % p for p in paths)
+    bad = str(tmp_path / "bad.fq")
+    open(bad, "wb").write(b"@r\nACGT\n+\nIIII\n\n")
+    r = subprocess.run([sys.executable, cli, bad], capture_output=True)
+    assert r.returncode == 1 and b"bad.fq" in r.stderr
+
+
+def test_full_size_properties(capi):
+    """BASELINE-sized batches (1M x 100 bp, 0.5M x 150 bp): every selected record is the
+    input record with an annotated header (round trip), order is preserved, counts agree
+    with the oracle on a prefix, and the pass is idempotent."""
+    from baitstr_b200 import synth
+    for cfg, L, kw in [(2, 100, {}), (3, 150, dict(n=3, rmhm=True))]:
+        n = 1000000 if L == 100 else 500000
+        raw = synth.generate(cfg, L, 0, n)
+        with capi.Context(want_results=True, **kw) as ctx:
+            out, info = ctx.scan_batch(raw)
+            out2, _ = ctx.scan_batch(raw)
+        assert out == out2 and info["n_records"] == n
+        rb = synth.record_bytes(cfg, L)
+        pre = 50000
+        want, wres = oracle.select_buffer(raw[:rb * pre].tobytes(), want_results=True, **kw)
+        assert out[:len(want)] == want
+        sel = info["results"][:, 2] != 0
+        assert int(sel.sum()) == info["n_selected"]
+        assert np.array_equal(sel[:pre], wres[:, 0] == 1)
+        lines = out.split(b"\n")
+        assert len(lines) == 4 * info["n_selected"] + 1 and lines[-1] == b""
+        recs = raw.tobytes().split(b"\n")
+        idx = np.nonzero(sel)[0]
+        step = max(1, len(idx) // 20000)
+        for j in range(0, len(idx), step):
+            r = int(idx[j])
+            hdr = lines[4 * j].split(b"\t")
+            assert hdr[0] == recs[4 * r] and len(hdr) == 9
+            assert lines[4 * j + 1] == recs[4 * r + 1].upper() and lines[4 * j + 3] == recs[4 * r + 3]
+            fs, fe = int(hdr[3]), int(hdr[4])
+            assert lines[4 * j + 1][fs:fs + len(hdr[1])] == hdr[1] and fe - fs == len(hdr[1]) * int(hdr[2])
