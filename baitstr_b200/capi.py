@@ -33,7 +33,8 @@ class BatchOut(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("records", C.c_uint64), ("selected", C.c_uint64), ("in_bytes", C.c_uint64),
-                ("out_bytes", C.c_uint64), ("batches", C.c_uint64), ("h2d_ms", C.c_double),
+                ("out_bytes", C.c_uint64), ("batches", C.c_uint64), ("fallback_batches", C.c_uint64),
+                ("h2d_ms", C.c_double),
                 ("kernel_ms", C.c_double), ("d2h_ms", C.c_double), ("wall_ms", C.c_double)]
 
 

@@ -1,0 +1,328 @@
+// fused.cuh -- the single-pass tile kernel of the select stage (sm_100a).
+//
+// One CTA owns FT_TILE bytes of raw FASTQ (plus FT_OVL bytes of look-ahead for the records
+// that start in its tile) staged in shared memory, and does everything the reference does
+// per record in one visit of the data:
+//   fastq.next()            /root/reference/src/fastq.pyx:72-94            (line split, checks)
+//   ProcessSequence         /root/reference/src/select_STR_reads.pyx:294-319 (both strands)
+//   PrintSequence           /root/reference/src/select_STR_reads.pyx:171-185 (annotated FASTQ)
+//   ordered output          /root/reference/src/select_STR_reads.pyx:363-367 (input order)
+// HBM traffic is the algorithmic minimum: every input byte is read once, every output
+// byte written once.  Tiles are chained by two decoupled look-backs (line count, output
+// bytes), tickets are handed out in launch order so a tile only ever waits for tiles that
+// already run.  Inputs the tile geometry cannot hold (records longer than FT_OVL, more
+// than FT_NLMAX lines in a tile, ...) raise BatchState::fallback and the host re-runs the
+// batch through the staged generic kernels (kernels_v1.cuh) -- still on the GPU.
+#pragma once
+#include <stdint.h>
+#include "kernels_v1.cuh"
+
+namespace bstr {
+
+constexpr int FT_THREADS = 256;
+constexpr int FT_TILE = 32768;                 // bytes owned by one tile
+constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
+constexpr int FT_REGION = FT_TILE + FT_OVL;
+constexpr int FT_CHUNKS = FT_REGION / 16;      // 16-byte chunks in the staged region
+constexpr int FT_CPT = FT_CHUNKS / FT_THREADS; // chunks per thread (contiguous)
+constexpr int FT_NLMAX = 2048;                 // line table entries
+constexpr int FT_RECMAX = 512;                 // records per tile
+constexpr int FT_STAGE = 40960;                // output staging bytes
+static_assert(FT_CHUNKS % FT_THREADS == 0, "region must split evenly over the threads");
+static_assert(FT_RECMAX == 2 * FT_THREADS, "offset scan assumes two records per thread");
+
+constexpr unsigned long long LB_MASK = (1ull << 62) - 1;
+constexpr unsigned long long LB_AGG = 1ull << 62;      // tile aggregate published
+constexpr unsigned long long LB_INC = 2ull << 62;      // inclusive prefix published
+
+struct FusedShared {
+    alignas(16) uint8_t in_raw[16 + FT_REGION + 32];    // tile bytes at in_raw + 16
+    alignas(16) uint8_t stage[FT_STAGE + 32];
+    uint16_t nl[FT_NLMAX + 8];                          // newline position + 1 (tile-relative)
+    ReadResult rec[FT_RECMAX];
+    uint32_t outoff[FT_RECMAX];                         // outlen, then exclusive offsets
+    uint32_t warp_tmp[FT_THREADS / 32];
+    long long gbase;                                    // global index of local line 0
+    unsigned long long out_base;
+    uint32_t tile, cnt_own, cnt_all, total_out, bail;
+};
+
+// Decoupled look-back, run by one full warp.  st[] was zeroed before the launch.  Returns
+// the exclusive prefix of `agg` over the tiles before `tile`.
+__device__ __forceinline__ unsigned long long warp_lookback(unsigned long long *st, int tile,
+                                                            unsigned long long agg)
+{
+    const int lane = threadIdx.x & 31;
+    if (tile == 0) {
+        if (lane == 0) atomicExch(&st[0], LB_INC | agg);
+        return 0;
+    }
+    if (lane == 0) atomicExch(&st[tile], LB_AGG | agg);
+    unsigned long long excl = 0;
+    int hi = tile - 1;
+    for (;;) {
+        const int p = hi - lane;
+        unsigned long long v = LB_INC;                   // before tile 0: inclusive 0
+        if (p >= 0) {
+            do { v = *(volatile unsigned long long *)&st[p]; } while ((v >> 62) == 0);
+        }
+        const unsigned inc = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2);
+        const int first = inc ? __ffs(inc) - 1 : 32;     // nearest predecessor with a prefix
+        unsigned long long c = (lane <= first) ? (v & LB_MASK) : 0ull;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, d);
+        excl += c;
+        if (inc) break;
+        hi -= 32;
+    }
+    if (lane == 0) atomicExch(&st[tile], LB_INC | (excl + agg));
+    return excl;
+}
+
+// 16-bit mask of the '\n' bytes of one 16-byte chunk
+__device__ __forceinline__ uint32_t nl_mask_of(const uint4 v)
+{
+    const uint32_t f0 = nl_flags(v.x), f1 = nl_flags(v.y), f2 = nl_flags(v.z), f3 = nl_flags(v.w);
+    return (((f0 >> 7) & 0x01010101u) * 0x01020408u >> 24) |
+           ((((f1 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 4) |
+           ((((f2 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 8) |
+           ((((f3 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 12);
+}
+
+// exclusive scan of one value per thread over the CTA; *total gets the sum
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_tmp, uint32_t *total)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    __syncthreads();                       // warp_tmp may still be read from a previous scan
+    if (lane == 31) warp_tmp[wid] = inc;
+    __syncthreads();
+    uint32_t wbase = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < FT_THREADS / 32; w++) {
+        const uint32_t x = warp_tmp[w];
+        if (w < wid) wbase += x;
+        tot += x;
+    }
+    *total = tot;
+    return wbase + inc - v;
+}
+
+__global__ void k_fused_init(BatchState *st, unsigned long long *lb, uint32_t n_lb_words)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_lb_words; i += gridDim.x * blockDim.x)
+        lb[i] = 0ull;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->first_bad = ~0ull; st->n_lines = 0; st->n_records = 0; st->n_selected = 0;
+        st->out_bytes = 0; st->consumed = 0; st->fallback = 0;
+    }
+}
+
+__device__ __forceinline__ RecordLines tile_record_lines(const uint16_t *nl, int i)
+{
+    RecordLines ln;
+    const uint32_t e0 = nl[i], e1 = nl[i + 1], e2 = nl[i + 2], e3 = nl[i + 3], e4 = nl[i + 4];
+    ln.s0 = e0; ln.e0 = e1 - 1; ln.s1 = e1; ln.e1 = e2 - 1;
+    ln.s2 = e2; ln.e2 = e3 - 1; ln.s3 = e3; ln.e3 = e4 - 1;
+    return ln;
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 2)
+k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
+             BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
+             unsigned long long *ticket, uint32_t ntiles, ReadResult *res, uint8_t *out,
+             uint64_t outcap)
+{
+    extern __shared__ __align__(16) uint8_t fused_smem[];
+    FusedShared &S = *reinterpret_cast<FusedShared *>(fused_smem);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) S.tile = (uint32_t)atomicAdd(ticket, 1ull);
+    if (tid < 4) {
+        reinterpret_cast<uint32_t *>(S.in_raw)[tid] = 0u;
+        reinterpret_cast<uint32_t *>(S.in_raw + 16 + FT_REGION)[tid] = 0u;
+        reinterpret_cast<uint32_t *>(S.in_raw + 16 + FT_REGION + 16)[tid] = 0u;
+    }
+    __syncthreads();
+    const uint32_t tile = S.tile;
+    const uint64_t ts = (uint64_t)tile * FT_TILE;
+    uint8_t *sin = S.in_raw + 16;
+    const bool reach = ts + FT_REGION >= n;          // the staged window covers the batch end
+    const bool last = tile == ntiles - 1;
+
+    // ---- A: stage the tile (+ look-ahead) in shared memory, 16-byte coalesced loads -------
+#pragma unroll
+    for (int i = 0; i < FT_CPT; i++) {
+        const int c = i * FT_THREADS + tid;
+        const uint64_t off = ts + 16ull * c;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (off < n) v = __ldg(reinterpret_cast<const uint4 *>(in + off));
+        *reinterpret_cast<uint4 *>(sin + 16 * c) = v;
+    }
+    __syncthreads();
+
+    // ---- B: line index of the window -----------------------------------------------------
+    uint32_t masks[FT_CPT];
+    uint32_t cnt = 0;                                // all << 16 | own
+#pragma unroll
+    for (int i = 0; i < FT_CPT; i++) {
+        const int c = tid * FT_CPT + i;
+        const uint64_t gpos = ts + 16ull * c;
+        uint32_t m = 0;
+        if (gpos < n) {
+            m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
+            const uint64_t rem = n - gpos;
+            if (rem < 16) m &= (1u << rem) - 1u;
+            // an unterminated last line: its last byte is dropped by line[:-1]
+            // (fastq.pyx:78,83,90), i.e. it plays the newline
+            if (final && rem <= 16) m |= 1u << (rem - 1);
+        }
+        masks[i] = m;
+        const uint32_t pc = __popc(m);
+        cnt += (pc << 16) | (c < FT_TILE / 16 ? pc : 0u);
+    }
+    uint32_t tot;
+    const uint32_t ex = block_excl_scan(cnt, S.warp_tmp, &tot);
+    const uint32_t shift = tile == 0 ? 1u : 0u;      // tile 0: virtual newline before byte 0
+    const uint32_t real_own = tot & 0xFFFFu;
+    uint32_t cnt_own = real_own + shift, cnt_all = (tot >> 16) + shift;
+    bool bail = cnt_all + 2 > FT_NLMAX;
+    {
+        uint32_t idx = (ex >> 16) + shift;
+#pragma unroll
+        for (int i = 0; i < FT_CPT; i++) {
+            uint32_t m = masks[i];
+            const uint32_t base = 16u * (tid * FT_CPT + i) + 1u;
+            while (m) {
+                const int b = __ffs(m) - 1;
+                m &= m - 1;
+                if (idx < FT_NLMAX) S.nl[idx] = (uint16_t)(base + b);
+                idx++;
+            }
+        }
+        if (tid == 0 && shift) S.nl[0] = 0;
+    }
+
+    // ---- C: global line number of the tile's first line (look-back #1) ---------------------
+    if (wid == 0) {
+        const unsigned long long base = warp_lookback(lb_lines, (int)tile, real_own);
+        if (lane == 0) S.gbase = tile == 0 ? -1ll : (long long)base;
+    }
+    __syncthreads();
+    const long long gbase = S.gbase;
+    const long long G = gbase + (long long)cnt_all;  // lines of the whole batch, if `reach`
+    if (final && reach && (G & 3) == 3 && !bail) {
+        // EOF after the separator line: accepted with an empty quality string
+        // (readline() returns '' at fastq.pyx:89)
+        if (tid == 0) S.nl[cnt_all] = (uint16_t)(n - ts + 1);
+        cnt_all++;
+    }
+    if (last && tid == 0) {
+        const unsigned long long lines = (unsigned long long)G + ((final && (G & 3) == 3) ? 1ull : 0ull);
+        st->n_lines = lines;
+        st->n_records = lines >> 2;
+        if (final) {
+            if ((G & 3) == 1 || (G & 3) == 2)        // file ends inside a record (fastq.pyx:86)
+                atomicMin(&st->first_bad, ((unsigned long long)(G >> 2) << 8) | BAD_TRUNCATED);
+            atomicMax(&st->consumed, (unsigned long long)n);
+        }
+    }
+    const uint32_t i0 = (uint32_t)((3 - gbase) & 3);
+    const uint32_t nrec_own = cnt_own > i0 ? (cnt_own - i0 + 3) / 4 : 0u;
+    uint32_t nproc = cnt_all >= i0 + 5 ? (cnt_all - 1 - i0) / 4 : 0u;
+    if (nproc > nrec_own) nproc = nrec_own;
+    if (nproc < nrec_own && !reach) bail = true;      // a record runs past the look-ahead
+    if (nproc > FT_RECMAX) bail = true;
+    if (!bail && nrec_own && tid == 0) {
+        const uint32_t iL = i0 + 4 * (nrec_own - 1);
+        if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + S.nl[iL]);
+    }
+    if (bail) nproc = 0;
+    __syncthreads();                                  // S.nl complete (virtual entry included)
+
+    // ---- D: per record: fastq.next() checks + both-strand match (thread per record) --------
+    uint32_t nsel = 0;
+    for (uint32_t jb = 0; jb < FT_RECMAX; jb += FT_THREADS) {
+        const uint32_t j = jb + tid;
+        const bool live = j < nproc;
+        if (jb >= nproc) {                            // CTA-uniform: nothing left in this round
+            S.outoff[j] = 0;
+            continue;
+        }
+        RecordLines ln = {};
+        int L = 0;
+        if (live) { ln = tile_record_lines(S.nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
+        const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
+        Hit f, rc;
+        f.k = rc.k = 0; f.copies = rc.copies = f.start = rc.start = 0;
+        bool sel = false;
+        uint32_t olen = 0;
+        if (live) {
+            const unsigned long long r = (unsigned long long)((gbase + (long long)(i0 + 4 * j) + 1) >> 2);
+            int bad = 0;
+            if (sin[ln.s0] != '@') bad = BAD_HEADER;                       // fastq.pyx:77
+            else if (bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
+            else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
+            if (bad) atomicMin(&st->first_bad, (r << 8) | (unsigned)bad);
+            else match_read(sin + ln.s1, L, prm, wmax, f, rc);
+            sel = f.k && rc.k;
+            ReadResult o;
+            o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : 0;
+            o.fck = sel ? ((uint32_t)f.copies << 3 | f.k) : 0;
+            o.rck = sel ? ((uint32_t)rc.copies << 3 | rc.k) : 0;
+            S.rec[j] = o;
+            if (res) res[r] = o;
+            if (sel) olen = record_out_len(ln.e0 - ln.s0 - 1, L, ln.e3 - ln.s3, f, rc);
+        }
+        S.outoff[j] = olen;
+        nsel += __popc(__ballot_sync(0xFFFFFFFFu, sel));
+    }
+    __syncthreads();
+
+    // ---- E: output offsets: records inside the tile, then the tile (look-back #2) ---------
+    const uint32_t o0 = S.outoff[2 * tid], o1 = S.outoff[2 * tid + 1];
+    uint32_t total;
+    const uint32_t oex = block_excl_scan(o0 + o1, S.warp_tmp, &total);
+    S.outoff[2 * tid] = oex;
+    S.outoff[2 * tid + 1] = oex + o0;
+    if (total > FT_STAGE - 16) { bail = true; total = 0; nproc = 0; }
+    if (bail && tid == 0) atomicExch(&st->fallback, 1ull);
+    if (wid == 0) {
+        const unsigned long long ob = warp_lookback(lb_out, (int)tile, total);
+        if (lane == 0) {
+            S.out_base = ob;
+            if (last) st->out_bytes = ob + total;
+        }
+    }
+    if (lane == 0 && nsel && !bail) atomicAdd(&st->n_selected, (unsigned long long)nsel);
+    __syncthreads();
+    const unsigned long long out_base = S.out_base;
+    if (total == 0 || out_base + total > outcap) return;     // host grows the buffer and re-runs
+
+    // ---- F: PrintSequence into the staging buffer (same 16-byte phase as the destination) --
+    const uint32_t a0 = (uint32_t)(out_base & 15);
+    for (uint32_t j = tid; j < nproc; j += FT_THREADS) {
+        const ReadResult rr = S.rec[j];
+        if (rr.fck == 0) continue;
+        const RecordLines ln = tile_record_lines(S.nl, (int)(i0 + 4 * j));
+        format_record(sin, ln, rr, illumina, S.stage + a0 + S.outoff[j]);
+    }
+    __syncthreads();
+
+    // ---- G: flush the staging buffer with aligned 16-byte stores ----------------------------
+    uint8_t *dst = out + out_base;
+    const uint32_t head = min(total, (16u - a0) & 15u);
+    if (tid < head) dst[tid] = S.stage[a0 + tid];
+    const uint32_t nchunk = (total - head) >> 4;
+    const uint8_t *sb = S.stage + a0 + head;
+    for (uint32_t c = tid; c < nchunk; c += FT_THREADS)
+        *reinterpret_cast<uint4 *>(dst + head + 16 * c) = *reinterpret_cast<const uint4 *>(sb + 16 * c);
+    const uint32_t done = head + (nchunk << 4);
+    if (tid < total - done) dst[done + tid] = S.stage[a0 + done + tid];
+}
+
+}  // namespace bstr

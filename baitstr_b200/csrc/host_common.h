@@ -19,12 +19,13 @@ constexpr size_t IN_SLACK = 64;    // readable bytes kept on both sides of a dev
 struct DeviceSlot {
     uint8_t *d_in_raw, *d_in;      // d_in = d_in_raw + IN_SLACK
     uint32_t *d_nlpos, *d_tiles, *d_outlen;
+    unsigned long long *d_lb;      // fused path: look-back words + ticket
     ReadResult *d_res;
     uint8_t *d_out;
     BatchState *d_state, *h_state;
     uint8_t *h_out;                // pinned
     ReadResult *h_res;             // pinned
-    size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres;
+    size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres, cap_lb;
 
     int reserve(struct ::bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need);
     void release();
@@ -36,6 +37,7 @@ struct bstr_ctx {
     bstr_params p;
     int dev;
     int sm_count;
+    bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
     cudaStream_t stream;
     cudaEvent_t ev[8];
     bstr::DeviceSlot slot;         // used by bstr_scan_batch / bstr_bench_resident
@@ -54,12 +56,12 @@ void set_error(bstr_ctx *ctx, const char *fmt, ...);
 int cuda_fail(bstr_ctx *ctx, cudaError_t e, const char *what, int line);
 struct ScanParams scan_params(const bstr_ctx *ctx);
 int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
-                    cudaEvent_t *ev);
+                    cudaEvent_t *ev, bool generic = false);
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record);
 void stream_release(bstr_ctx *ctx);
-int pipeline_stage_count();
-const char *pipeline_stage_name(int k);
-int pipeline_launches_per_batch();
+int pipeline_stage_count(const bstr_ctx *ctx);
+const char *pipeline_stage_name(const bstr_ctx *ctx, int k);
+int pipeline_launches_per_batch(const bstr_ctx *ctx);
 constexpr int BSTR_MAX_STAGES = 8;
 
 #define CUDA_TRY(call)                                                          \

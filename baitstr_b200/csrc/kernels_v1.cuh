@@ -23,6 +23,7 @@ struct BatchState {                 // lives in device memory, one per in-flight
     unsigned long long n_selected;
     unsigned long long out_bytes;
     unsigned long long consumed;
+    unsigned long long fallback;    // fused path only: input needs the generic kernels
 };
 
 enum { BAD_HEADER = 1, BAD_BASES = 2, BAD_SEPARATOR = 3, BAD_TRUNCATED = 4 };
@@ -181,6 +182,7 @@ __global__ void k_finish_index(uint32_t *nlpos, const unsigned long long *n_newl
     st->consumed = final ? n : (nrec ? (unsigned long long)nlpos[4 * nrec - 1] + 1 : 0);
     st->n_selected = 0;
     st->out_bytes = 0;
+    st->fallback = 0;
 }
 
 __device__ __forceinline__ bool base_ok(uint8_t b)

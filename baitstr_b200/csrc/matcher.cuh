@@ -599,4 +599,38 @@ __device__ __forceinline__ void match_read(const uint8_t *seq, int L, const Scan
     else match_read_bytes(seq, L, prm, fwd, rc);
 }
 
+// Bit 0 of every byte lane of the result is set iff that byte is NOT one of acgtnACGTN.
+// (fastq.pyx:62-67); the other bits are don't-care.  Derivation in DESIGN.md: with x_i =
+// bit i of the byte, T = x2&~x1&~x3 (only 'T' has it), a valid byte has x7 = 0,
+// x4 = T, x0 = ~x3&~T, x3 -> x2&x1, and x6 = 1 unless it is '.' (x3 & x5).
+__device__ __forceinline__ uint32_t swar_invalid(uint32_t w)
+{
+    const uint32_t s1 = w >> 1, s2 = w >> 2, s3 = w >> 3, s4 = w >> 4, s5 = w >> 5, s6 = w >> 6,
+                   s7 = w >> 7;
+    const uint32_t t = s2 & ~s1 & ~s3;
+    const uint32_t b = s3 & ~(s2 & s1);
+    const uint32_t c = (s4 ^ t) | b;
+    const uint32_t d = w ^ (~s3 & ~t);
+    const uint32_t e = ~s6 & ~(s3 & s5);
+    return c | d | e | s7;
+}
+
+// Any byte of [p, p+L) outside acgtnACGTN. ?  Reads whole aligned words around the range.
+__device__ __forceinline__ bool bases_invalid(const uint8_t *p, int L)
+{
+    const uintptr_t a = (uintptr_t)p;
+    const uint32_t *wp = (const uint32_t *)(a & ~(uintptr_t)3);
+    const int head = (int)(a & 3), total = head + L, nw = (total + 3) >> 2;
+    uint32_t acc = 0;
+    for (int i = 0; i < nw; i++) {
+        uint32_t w = wp[i], m = 0xFFFFFFFFu;
+        if (i == 0) m <<= 8 * head;
+        const int r = total - 4 * i;
+        if (r < 4) m &= (1u << (8 * r)) - 1u;
+        w = (w & m) | (0x41414141u & ~m);
+        acc |= swar_invalid(w);
+    }
+    return (acc & 0x01010101u) != 0;
+}
+
 }  // namespace bstr

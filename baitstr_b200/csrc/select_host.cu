@@ -13,6 +13,7 @@
 
 #include "host_common.h"
 #include "kernels_v1.cuh"
+#include "fused.cuh"
 
 namespace bstr {
 
@@ -58,6 +59,8 @@ int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
     GROW(d_outlen, cap_outlen, max_rec * 4, false);
     if (out_need < 2 * nbytes + 4096) out_need = 2 * nbytes + 4096;
     GROW(d_out, cap_out, out_need, false);
+    const uint64_t n_tiles_f = nbytes / FT_TILE + 2;
+    GROW(d_lb, cap_lb, (2 * n_tiles_f + 2) * 8, false);
     if (!d_state) {
         CUDA_TRY(cudaMalloc((void **)&d_state, sizeof(BatchState) + 64));
         CUDA_TRY(cudaHostAlloc((void **)&h_state, sizeof(BatchState), cudaHostAllocDefault));
@@ -68,7 +71,7 @@ int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
 void DeviceSlot::release()
 {
     cudaFree(d_in_raw); cudaFree(d_nlpos); cudaFree(d_tiles); cudaFree(d_res);
-    cudaFree(d_outlen); cudaFree(d_out); cudaFree(d_state);
+    cudaFree(d_outlen); cudaFree(d_out); cudaFree(d_state); cudaFree(d_lb);
     if (h_state) cudaFreeHost(h_state);
     if (h_out) cudaFreeHost(h_out);
     if (h_res) cudaFreeHost(h_res);
@@ -86,9 +89,9 @@ ScanParams scan_params(const bstr_ctx *ctx)
     return s;
 }
 
-// Launch the device pipeline for the nbytes at slot.d_in.  Nothing here synchronises.
-int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
-                    cudaEvent_t *ev /* 6 events or NULL */)
+// The staged generic pipeline (kernels_v1.cuh): any input, four passes over the data.
+static int launch_generic(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
+                          cudaEvent_t *ev /* 5 events or NULL */)
 {
     const ScanParams prm = scan_params(ctx);
     const unsigned n_tiles = (unsigned)((nbytes + IDX_TILE - 1) / IDX_TILE);
@@ -111,13 +114,44 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
     return BSTR_OK;
 }
 
-int pipeline_stage_count() { return 4; }
-const char *pipeline_stage_name(int k)
+// The fused single-pass tile kernel (fused.cuh).  Sets BatchState::fallback when the input
+// does not fit the tile geometry; the caller then runs launch_generic on the same slot.
+static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
+                        cudaEvent_t *ev)
 {
-    static const char *names[4] = {"index(newlines)", "k_scan_records", "k_scan_outlen", "k_format_records"};
-    return names[k];
+    const ScanParams prm = scan_params(ctx);
+    const uint32_t n_tiles = (uint32_t)((nbytes + FT_TILE - 1) / FT_TILE);
+    unsigned long long *lb_lines = s.d_lb, *lb_out = s.d_lb + n_tiles, *ticket = s.d_lb + 2 * (size_t)n_tiles;
+    const uint32_t lb_words = 2 * n_tiles + 1;
+    const uint32_t init_blocks = (lb_words + 255) / 256 < 64 ? (lb_words + 255) / 256 : 64;
+    if (ev) cudaEventRecord(ev[0], st);
+    k_fused_init<<<init_blocks, 256, 0, st>>>(s.d_state, s.d_lb, lb_words);
+    if (ev) cudaEventRecord(ev[1], st);
+    if (n_tiles)
+        k_fused_tile<<<n_tiles, FT_THREADS, sizeof(FusedShared), st>>>(
+            s.d_in, nbytes, final, prm, ctx->p.illumina_quals, s.d_state, lb_lines, lb_out, ticket,
+            n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out);
+    if (ev) { cudaEventRecord(ev[2], st); cudaEventRecord(ev[4], st); }
+    CUDA_TRY(cudaGetLastError());
+    return BSTR_OK;
 }
-int pipeline_launches_per_batch() { return 7; }
+
+// Launch the device pipeline for the nbytes at slot.d_in.  Nothing here synchronises.
+int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
+                    cudaEvent_t *ev, bool generic)
+{
+    return (generic || ctx->force_generic) ? launch_generic(ctx, s, nbytes, final, st, ev)
+                                           : launch_fused(ctx, s, nbytes, final, st, ev);
+}
+
+int pipeline_stage_count(const bstr_ctx *ctx) { return ctx->force_generic ? 4 : 2; }
+const char *pipeline_stage_name(const bstr_ctx *ctx, int k)
+{
+    static const char *gen[4] = {"index(newlines)", "k_scan_records", "k_scan_outlen", "k_format_records"};
+    static const char *fus[2] = {"k_fused_init", "k_fused_tile"};
+    return ctx->force_generic ? gen[k] : fus[k];
+}
+int pipeline_launches_per_batch(const bstr_ctx *ctx) { return ctx->force_generic ? 7 : 2; }
 
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record)
 {
@@ -189,6 +223,16 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     }
     ctx->sm_count = prop.multiProcessorCount;
     ctx->bench_slots = new std::vector<DeviceSlot>();
+    {
+        const char *fg = getenv("BSTR_FORCE_GENERIC");
+        ctx->force_generic = fg && fg[0] == '1';
+    }
+    e = cudaFuncSetAttribute(k_fused_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FusedShared));
+    if (e != cudaSuccess) {
+        if (err && errlen) snprintf(err, errlen, "bstr_create: %s", cudaGetErrorString(e));
+        bstr_destroy(ctx);
+        return nullptr;
+    }
     for (int i = 0; i < 8; i++) cudaEventCreate(&ctx->ev[i]);
     return ctx;
 }

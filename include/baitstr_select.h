@@ -81,6 +81,7 @@ typedef struct bstr_batch_out {
 
 typedef struct bstr_stats {
     uint64_t records, selected, in_bytes, out_bytes, batches;
+    uint64_t fallback_batches;                     /* batches re-run through the generic kernels */
     double h2d_ms, kernel_ms, d2h_ms, wall_ms;     /* summed over batches (CUDA events)      */
 } bstr_stats;
 

@@ -35,6 +35,8 @@ def lib():
         _lib.emul_match_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(Params),
                                           C.c_int, C.c_void_p]
         _lib.emul_match_reads.restype = None
+        _lib.emul_bases_invalid.argtypes = [C.c_char_p, C.c_int]
+        _lib.emul_bases_invalid.restype = C.c_int
     return _lib
 
 
@@ -51,3 +53,8 @@ def match_reads(seqs, n=2, f=31, ks=None, rmhm=False, altalgo=True, force_w=0):
     lib().emul_match_reads(blob.ctypes.data, off.ctypes.data, len(seqs), C.byref(p), force_w,
                            res.ctypes.data)
     return res
+
+
+def bases_invalid(data, misalign=0):
+    buf = C.create_string_buffer(b"\0" * misalign + bytes(data))
+    return bool(lib().emul_bases_invalid(C.cast(C.addressof(buf) + misalign, C.c_char_p), len(data)))

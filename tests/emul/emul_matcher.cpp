@@ -67,4 +67,17 @@ void emul_match_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, cons
         free(buf);
     }
 }
+
+// exhaustive check hook for the SWAR base validator: returns 1 if the device code calls the
+// L bytes at p (any alignment) invalid
+int emul_bases_invalid(const uint8_t *p, int L)
+{
+    uint8_t *buf = (uint8_t *)calloc((size_t)L + 64, 1);
+    memset(buf, 0xEE, (size_t)L + 64);                 // poison around the range
+    uint8_t *s = buf + 16 + ((uintptr_t)p & 3);
+    memcpy(s, p, (size_t)L);
+    const int r = bstr::bases_invalid(s, L) ? 1 : 0;
+    free(buf);
+    return r;
+}
 }

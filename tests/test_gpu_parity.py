@@ -267,3 +267,62 @@ def test_full_size_properties(capi):
             assert lines[4 * j + 1] == recs[4 * r + 1].upper() and lines[4 * j + 3] == recs[4 * r + 3]
             fs, fe = int(hdr[3]), int(hdr[4])
             assert lines[4 * j + 1][fs:fs + len(hdr[1])] == hdr[1] and fe - fs == len(hdr[1]) * int(hdr[2])
+
+
+def test_generic_kernels_forced(capi, monkeypatch):
+    """The staged generic kernels (the fused kernel's fallback) stay byte-exact on their own."""
+    monkeypatch.setenv("BSTR_FORCE_GENERIC", "1")
+    raw = util.synth_fastq(5000, 150, seed=77, p_str=0.6, p_n=0.1, vary_len=True, p_dot=0.02)
+    for kw in (dict(), dict(n=3, rmhm=True), dict(altalgo=False, f=10)):
+        with capi.Context(**kw) as ctx:
+            assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, **kw)
+    man = util.manifest()["testdata_default"]
+    with capi.Context() as ctx:
+        out = b"".join(ctx.scan_batch(util.gz_read("testdata_%d.fq.gz" % i))[0] for i in (1, 2))
+    assert hashlib.md5(out).hexdigest() == man["md5"]
+
+
+def test_fused_tile_geometry_and_fallback(capi):
+    """Records crossing tile boundaries at every phase, and inputs the tile geometry cannot
+    hold (very long reads, thousands of tiny records per tile) which must take the generic
+    kernels and still be byte-exact."""
+    rng = random.Random(99)
+    # (a) many tiles, ragged record sizes: every boundary alignment occurs
+    raw = util.synth_fastq(60000, 300, seed=123, p_str=0.5, p_n=0.05, vary_len=True)
+    with capi.Context(want_results=True) as ctx:
+        got, info = ctx.scan_batch(raw)
+        assert got == oracle.select_buffer(raw)
+        assert ctx.stats()["fallback_batches"] == 0
+        # (b) non-final cut in the middle of a record, many tiles
+        cut = len(raw) // 2 + 57
+        g1, i1 = ctx.scan_batch(raw[:cut], final=False)
+        g2, i2 = ctx.scan_batch(raw[i1["consumed"]:], final=True)
+        assert g1 + g2 == got and i1["n_records"] + i2["n_records"] == 60000
+    # (c) reads longer than the look-ahead window
+    recs = []
+    for i in range(300):
+        L = rng.choice([100, 3000, 5000, 9000, 40000])
+        s = "".join(rng.choice("ACGT") for _ in range(L))
+        p = rng.randrange(0, L - 40)
+        s = s[:p] + "CAG" * 10 + s[p + 30:]
+        recs.append("@long%d\n%s\n+\n%s\n" % (i, s, "I" * L))
+    raw = "".join(recs).encode()
+    with capi.Context() as ctx:
+        assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw)
+        assert ctx.stats()["fallback_batches"] == 1
+    # (d) tiny records: more lines per tile than the line table holds
+    raw = b"".join(b"@%d\nACACAC\n+\nIIIIII\n" % i for i in range(20000))
+    with capi.Context(n=2, f=1) as ctx:
+        assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, n=2, f=1)
+        assert ctx.stats()["fallback_batches"] == 1
+    # (e) degenerate: newlines only / no newline at all (errors must agree with the oracle)
+    for raw in (b"\n" * 100000, b"A" * 100000, b"@x\n" + b"A" * 70000 + b"\n+\n" + b"I" * 70000):
+        with capi.Context() as ctx:
+            try:
+                want = oracle.select_buffer(raw)
+            except oracle.OracleError as oe:
+                with pytest.raises(capi.BstrError) as ei:
+                    ctx.scan_batch(raw)
+                assert ei.value.code == ERRMAP[oe.code] and ei.value.bad_record == oe.record
+            else:
+                assert ctx.scan_batch(raw)[0] == want

@@ -92,3 +92,17 @@ def test_fuzz_goldens_from_reference():
             else:
                 want = (fwd[2], rc[2], fwd[1] << 3 | len(fwd[0]), rc[1] << 3 | len(rc[0]))
             assert tuple(int(x) for x in g) == want, c
+
+
+def test_swar_base_validator_exhaustive():
+    """fastq.pyx:62-67: every byte value, every alignment and position in a word."""
+    ok = set(b"acgtnACGTN.")
+    for mis in range(4):
+        for L in (1, 2, 3, 4, 5, 7, 8, 9, 33):
+            assert not emul.bases_invalid(b"ACGTNacgtn."[:L] * 1 if L <= 11 else b"ACGT.nN" * 5, mis)
+            for pos in {0, L // 2, L - 1}:
+                for b in range(256):
+                    s = bytearray((b"ACGTN.acgtn" * 4)[:L])
+                    s[pos] = b
+                    assert emul.bases_invalid(bytes(s), mis) == (b not in ok), (mis, L, pos, b)
+    assert not emul.bases_invalid(b"", 1)
