@@ -241,6 +241,17 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
         const uint32_t iL = i0 + 4 * (nrec_own - 1);
         if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + S.nl[iL]);
     }
+    if (!bail && final && reach && nproc < nrec_own && tid == 0) {
+        // a record cut short by EOF: the reference still tests its header (fastq.pyx:77) and a
+        // complete second line (fastq.pyx:81) before the missing line raises (fastq.pyx:86)
+        const uint32_t i = i0 + 4 * nproc, after = cnt_all - 1 - i;
+        if (after >= 1) {
+            const unsigned long long r = (unsigned long long)(G >> 2);
+            if (sin[S.nl[i]] != '@') atomicMin(&st->first_bad, (r << 8) | BAD_HEADER);
+            else if (after >= 2 && bases_invalid(sin + S.nl[i + 1], (int)S.nl[i + 2] - 1 - (int)S.nl[i + 1]))
+                atomicMin(&st->first_bad, (r << 8) | BAD_BASES);
+        }
+    }
     if (bail) nproc = 0;
     __syncthreads();                                  // S.nl complete (virtual entry included)
 

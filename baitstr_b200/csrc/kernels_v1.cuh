@@ -154,41 +154,57 @@ k_fill_newlines(const uint8_t *in, uint64_t n, const uint32_t *tile_prefix, uint
 // After the line index: number of lines / records the batch holds.
 //   final batch, last byte not '\n': the last char of the unterminated line is dropped by
 //   the reference's line[:-1] (fastq.pyx:78,83,90), i.e. it acts as that line's newline.
-__global__ void k_finish_index(uint32_t *nlpos, const unsigned long long *n_newlines,
-                               const uint8_t *in, uint64_t n, int final, BatchState *st)
-{
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long lines = *n_newlines;
-    if (final && n > 0 && in[n - 1] != '\n') {
-        nlpos[lines] = (uint32_t)(n - 1);
-        lines++;
-    }
-    unsigned long long nrec = lines / 4;
-    st->first_bad = ~0ull;
-    if (final && (lines & 3)) {
-        // EOF inside a record.  1 line (header only) or 2 lines (no separator) is the
-        // reference's IndexError at fastq.pyx:86; 3 lines (separator present, quality
-        // line missing) is ACCEPTED with an empty quality string (readline() returns '').
-        if ((lines & 3) == 3) {
-            nlpos[lines] = (uint32_t)n;          // empty 4th line: start == end == n
-            lines++;
-            nrec++;
-        } else {
-            st->first_bad = (nrec << 8) | BAD_TRUNCATED;
-        }
-    }
-    st->n_lines = lines;
-    st->n_records = nrec;
-    st->consumed = final ? n : (nrec ? (unsigned long long)nlpos[4 * nrec - 1] + 1 : 0);
-    st->n_selected = 0;
-    st->out_bytes = 0;
-    st->fallback = 0;
-}
-
 __device__ __forceinline__ bool base_ok(uint8_t b)
 {   // fastq.pyx:65
     const uint8_t u = b & 0xDF;     // clear bit 5: upper-case letters; '.' (0x2E) -> 0x0E
     return u == 'A' || u == 'C' || u == 'G' || u == 'T' || u == 'N' || b == '.';
+}
+
+// One block.  A record cut short by EOF still gets the reference's earlier checks first:
+// header '@' (fastq.pyx:77) and the bases of a complete second line (fastq.pyx:81) are
+// tested before the missing separator raises (fastq.pyx:86), so those errors win.
+__global__ void k_finish_index(uint32_t *nlpos, const unsigned long long *n_newlines,
+                               const uint8_t *in, uint64_t n, int final, BatchState *st)
+{
+    __shared__ uint32_t s_b0, s_b1;
+    __shared__ unsigned long long s_rec;
+    if (threadIdx.x == 0) {
+        s_b0 = s_b1 = 0;
+        unsigned long long lines = *n_newlines;
+        if (final && n > 0 && in[n - 1] != '\n') {
+            nlpos[lines] = (uint32_t)(n - 1);
+            lines++;
+        }
+        unsigned long long nrec = lines / 4;
+        st->first_bad = ~0ull;
+        if (final && (lines & 3)) {
+            // EOF inside a record.  1 line (header only) or 2 lines (no separator) is the
+            // reference's IndexError at fastq.pyx:86; 3 lines (separator present, quality
+            // line missing) is ACCEPTED with an empty quality string (readline() returns '').
+            if ((lines & 3) == 3) {
+                nlpos[lines] = (uint32_t)n;          // empty 4th line: start == end == n
+                lines++;
+                nrec++;
+            } else {
+                unsigned long long code = BAD_TRUNCATED;
+                const uint32_t s0 = nrec ? nlpos[4 * nrec - 1] + 1 : 0;
+                if (in[s0] != '@') code = BAD_HEADER;
+                else if ((lines & 3) == 2) { s_b0 = nlpos[4 * nrec] + 1; s_b1 = nlpos[4 * nrec + 1]; }
+                st->first_bad = (nrec << 8) | code;
+                s_rec = nrec;
+            }
+        }
+        st->n_lines = lines;
+        st->n_records = nrec;
+        st->consumed = final ? n : (nrec ? (unsigned long long)nlpos[4 * nrec - 1] + 1 : 0);
+        st->n_selected = 0;
+        st->out_bytes = 0;
+        st->fallback = 0;
+    }
+    __syncthreads();
+    bool bad = false;
+    for (uint32_t i = s_b0 + threadIdx.x; i < s_b1; i += blockDim.x) bad |= !base_ok(in[i]);
+    if (bad) atomicMin(&st->first_bad, (s_rec << 8) | BAD_BASES);
 }
 
 __device__ __forceinline__ int dec_digits(uint32_t v)

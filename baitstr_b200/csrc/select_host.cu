@@ -101,7 +101,7 @@ static int launch_generic(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int fin
     if (n_tiles) k_count_newlines<<<n_tiles, IDX_THREADS, 0, st>>>(s.d_in, nbytes, s.d_tiles);
     k_exclusive_scan<<<1, 1024, 0, st>>>(s.d_tiles, n_tiles, d_total);
     if (n_tiles) k_fill_newlines<<<n_tiles, IDX_THREADS, 0, st>>>(s.d_in, nbytes, s.d_tiles, s.d_nlpos);
-    k_finish_index<<<1, 32, 0, st>>>(s.d_nlpos, d_total, s.d_in, nbytes, final, s.d_state);
+    k_finish_index<<<1, 256, 0, st>>>(s.d_nlpos, d_total, s.d_in, nbytes, final, s.d_state);
     if (ev) cudaEventRecord(ev[1], st);
     k_scan_records<<<rec_blocks, 128, 0, st>>>(s.d_in, s.d_nlpos, s.d_state, prm, s.d_res, s.d_outlen);
     if (ev) cudaEventRecord(ev[2], st);

@@ -316,7 +316,11 @@ def test_fused_tile_geometry_and_fallback(capi):
         assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, n=2, f=1)
         assert ctx.stats()["fallback_batches"] == 1
     # (e) degenerate: newlines only / no newline at all (errors must agree with the oracle)
-    for raw in (b"\n" * 100000, b"A" * 100000, b"@x\n" + b"A" * 70000 + b"\n+\n" + b"I" * 70000):
+    good = util.synth_fastq(700, 100, seed=3)
+    for raw in (b"\n" * 100000, b"A" * 100000, b"@x\n" + b"A" * 70000 + b"\n+\n" + b"I" * 70000,
+                b"@x\nACGT\n", b"x\nACGT", b"@x\nACRT\n", b"@x\nACRT", b"@x", b"@x\nACGT\n+",
+                good + b"@x\nACGT\n", good + b"x\nACGT", good + b"@x\nACRT\n", good + b"@x\nACR",
+                good + b"@x\nACGT\n+", good + b"@x\nACGT\n+\n", good + b"@x\nACGT\n-"):
         with capi.Context() as ctx:
             try:
                 want = oracle.select_buffer(raw)
