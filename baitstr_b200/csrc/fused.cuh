@@ -82,11 +82,11 @@ __device__ __forceinline__ unsigned long long warp_lookback(unsigned long long *
 // 16-bit mask of the '\n' bytes of one 16-byte chunk
 __device__ __forceinline__ uint32_t nl_mask_of(const uint4 v)
 {
-    const uint32_t f0 = nl_flags(v.x), f1 = nl_flags(v.y), f2 = nl_flags(v.z), f3 = nl_flags(v.w);
-    return (((f0 >> 7) & 0x01010101u) * 0x01020408u >> 24) |
-           ((((f1 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 4) |
-           ((((f2 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 8) |
-           ((((f3 >> 7) & 0x01010101u) * 0x01020408u >> 24) << 12);
+    // nl_flags leaves 0x80 in every newline byte; dp4a with weights 1,2,4,8 / 16..128 packs
+    // eight of them into one byte (scaled by 128)
+    const uint32_t lo = __dp4a(nl_flags(v.y), 0x80402010u, __dp4a(nl_flags(v.x), 0x08040201u, 0u));
+    const uint32_t hi = __dp4a(nl_flags(v.w), 0x80402010u, __dp4a(nl_flags(v.z), 0x08040201u, 0u));
+    return (lo >> 7) | (hi << 1);
 }
 
 // exclusive scan of one value per thread over the CTA; *total gets the sum
@@ -130,6 +130,69 @@ __device__ __forceinline__ RecordLines tile_record_lines(const uint16_t *nl, int
     ln.s0 = e0; ln.e0 = e1 - 1; ln.s1 = e1; ln.e1 = e2 - 1;
     ln.s2 = e2; ln.e2 = e3 - 1; ln.s3 = e3; ln.e3 = e4 - 1;
     return ln;
+}
+
+// ---- PrintSequence (select_STR_reads.pyx:171-185) into shared memory, word-granular -------
+enum { XF_NONE = 0, XF_UPPER = 1, XF_MINUS31 = 2 };
+
+template <int MODE> __device__ __forceinline__ uint32_t xform_word(uint32_t w)
+{
+    if (MODE == XF_UPPER) return w & ~((w & 0x40404040u) >> 1);     // letters: clear bit 5 (fastq.pyx:83)
+    if (MODE == XF_MINUS31)                                        // per-byte x - 31 (pyx:181), no borrows
+        return ((w | 0x80808080u) - 0x1F1F1F1Fu) ^ (~w & 0x80808080u);
+    return w;
+}
+template <int MODE> __device__ __forceinline__ uint8_t xform_byte(uint8_t c)
+{
+    if (MODE == XF_UPPER) return (c & 0x40) ? (uint8_t)(c & 0xDF) : c;
+    if (MODE == XF_MINUS31) return (uint8_t)(c - 31);
+    return c;
+}
+
+// copy n bytes s -> d (both shared memory, any alignment) with aligned 32-bit stores
+template <int MODE>
+__device__ __forceinline__ uint8_t *copy_xform(uint8_t *d, const uint8_t *s, int n)
+{
+    while (n > 0 && ((uintptr_t)d & 3)) { *d++ = xform_byte<MODE>(*s++); n--; }
+    const int nw = n >> 2;
+    if (nw > 0) {
+        const uint32_t *sp = (const uint32_t *)((uintptr_t)s & ~(uintptr_t)3);
+        const int sh = (int)((uintptr_t)s & 3) * 8;
+        uint32_t *dp = (uint32_t *)d;
+        uint32_t lo = sp[0];
+        for (int i = 0; i < nw; i++) {
+            const uint32_t hi = sp[i + 1];
+            dp[i] = xform_word<MODE>(__funnelshift_r(lo, hi, sh));
+            lo = hi;
+        }
+        d += 4 * nw; s += 4 * nw; n -= 4 * nw;
+    }
+    while (n > 0) { *d++ = xform_byte<MODE>(*s++); n--; }
+    return d;
+}
+
+__device__ __forceinline__ void format_record_words(const uint8_t *in, const RecordLines &ln,
+                                                    const ReadResult &rr, int illumina, uint8_t *p)
+{
+    const int L = (int)(ln.e1 - ln.s1);
+    const int fk = rr.fck & 7, fc = rr.fck >> 3, rk = rr.rck & 7, rcn = rr.rck >> 3;
+    p = copy_xform<XF_NONE>(p, in + ln.s0, (int)(ln.e0 - ln.s0));          // '@' + name (validated)
+    *p++ = '\t';
+    for (int j = 0; j < fk; j++) *p++ = upper(in[ln.s1 + rr.fstart + j]);
+    *p++ = '\t'; p = put_dec(p, fc);
+    *p++ = '\t'; p = put_dec(p, rr.fstart);
+    *p++ = '\t'; p = put_dec(p, rr.fstart + fk * fc);
+    *p++ = '\t';
+    for (int j = 0; j < rk; j++) *p++ = comp_base(upper(in[ln.s1 + (L - 1 - (int)rr.rstart - j)]));
+    *p++ = '\t'; p = put_dec(p, rcn);
+    *p++ = '\t'; p = put_dec(p, rr.rstart);
+    *p++ = '\t'; p = put_dec(p, rr.rstart + rk * rcn);
+    *p++ = '\n';
+    p = copy_xform<XF_UPPER>(p, in + ln.s1, L);
+    *p++ = '\n'; *p++ = '+'; *p++ = '\n';
+    const int Q = (int)(ln.e3 - ln.s3);
+    p = illumina ? copy_xform<XF_MINUS31>(p, in + ln.s3, Q) : copy_xform<XF_NONE>(p, in + ln.s3, Q);
+    *p++ = '\n';
 }
 
 __global__ void __launch_bounds__(FT_THREADS, 2)
@@ -320,7 +383,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
         const ReadResult rr = S.rec[j];
         if (rr.fck == 0) continue;
         const RecordLines ln = tile_record_lines(S.nl, (int)(i0 + 4 * j));
-        format_record(sin, ln, rr, illumina, S.stage + a0 + S.outoff[j]);
+        format_record_words(sin, ln, rr, illumina, S.stage + a0 + S.outoff[j]);
     }
     __syncthreads();
 

@@ -478,21 +478,25 @@ __device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const
     if (Gn <= 0 || end_max - sh < 2 * n) return;
     const bool use_hm = prm.altalgo && prm.rmhm;
 
-    Planes<W> P;
-    Bits<W> nmask;
-    encode_window<W>(seq + g0, Gn, P, nmask);
-    Planes<W> R = P;
-    Bits<W> rn = nmask;
-    mark_invalid(P, Gn);
-    uint64_t kf = strand_best<W>(P, nmask, sh, end_max, n, prm.kmask, use_hm);
-    if (!prm.altalgo) kf = xalgo_filter<W>(kf, prm, L);
-    if (kf == 0) return;                             // ProcessSequence: fwd None -> drop
-    revcomp_planes(R, rn, Gn);
-    mark_invalid(R, Gn);
-    uint64_t kr = strand_best<W>(R, rn, sh, end_max, n, prm.kmask, use_hm);
-    if (!prm.altalgo) kr = xalgo_filter<W>(kr, prm, L);
-    fwd = unpack_hit(kf, g0);
-    rc = unpack_hit(kr, g0);
+    Planes<W> raw;
+    Bits<W> rawn;
+    encode_window<W>(seq + g0, Gn, raw, rawn);
+    uint64_t key0 = 0, key1 = 0;
+    // one copy of the strand code, run twice (keeps the kernel inside the instruction cache)
+#pragma unroll 1
+    for (int strand = 0; strand < 2; strand++) {
+        Planes<W> Q = raw;
+        Bits<W> qn = rawn;
+        if (strand) revcomp_planes(Q, qn, Gn);       // ReverseComplement, pyx:187-189
+        mark_invalid(Q, Gn);
+        uint64_t k = strand_best<W>(Q, qn, sh, end_max, n, prm.kmask, use_hm);
+        if (!prm.altalgo) k = xalgo_filter<W>(k, prm, L);
+        if (strand) key1 = k; else key0 = k;
+        if (k == 0) break;                           // ProcessSequence: a strand with None drops the read
+    }
+    if (key0 == 0) return;
+    fwd = unpack_hit(key0, g0);
+    rc = unpack_hit(key1, g0);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -620,15 +624,20 @@ __device__ __forceinline__ bool bases_invalid(const uint8_t *p, int L)
 {
     const uintptr_t a = (uintptr_t)p;
     const uint32_t *wp = (const uint32_t *)(a & ~(uintptr_t)3);
+    if (L <= 0) return false;
     const int head = (int)(a & 3), total = head + L, nw = (total + 3) >> 2;
-    uint32_t acc = 0;
-    for (int i = 0; i < nw; i++) {
-        uint32_t w = wp[i], m = 0xFFFFFFFFu;
-        if (i == 0) m <<= 8 * head;
-        const int r = total - 4 * i;
-        if (r < 4) m &= (1u << (8 * r)) - 1u;
-        w = (w & m) | (0x41414141u & ~m);
-        acc |= swar_invalid(w);
+    // bytes outside the range are replaced by 'A'; only the first and last word need it
+    const uint32_t mfirst = 0xFFFFFFFFu << (8 * head);
+    const int r = total - 4 * (nw - 1);                        // 1..4 bytes in the last word
+    const uint32_t mlast = r < 4 ? (1u << (8 * r)) - 1u : 0xFFFFFFFFu;
+    uint32_t acc;
+    if (nw == 1) {
+        const uint32_t m = mfirst & mlast;
+        acc = swar_invalid((wp[0] & m) | (0x41414141u & ~m));
+    } else {
+        acc = swar_invalid((wp[0] & mfirst) | (0x41414141u & ~mfirst));
+        for (int i = 1; i < nw - 1; i++) acc |= swar_invalid(wp[i]);
+        acc |= swar_invalid((wp[nw - 1] & mlast) | (0x41414141u & ~mlast));
     }
     return (acc & 0x01010101u) != 0;
 }
