@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(FT_THREADS, 2)
 k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
              BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
              unsigned long long *ticket, uint32_t ntiles, ReadResult *res, uint8_t *out,
-             uint64_t outcap)
+             uint64_t outcap, int exp_mask)
 {
     extern __shared__ __align__(16) uint8_t fused_smem[];
     FusedShared &S = *reinterpret_cast<FusedShared *>(fused_smem);
@@ -339,10 +339,10 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
             const unsigned long long r = (unsigned long long)((gbase + (long long)(i0 + 4 * j) + 1) >> 2);
             int bad = 0;
             if (sin[ln.s0] != '@') bad = BAD_HEADER;                       // fastq.pyx:77
-            else if (bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
+            else if (!(exp_mask & 2) && bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
             else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
             if (bad) atomicMin(&st->first_bad, (r << 8) | (unsigned)bad);
-            else match_read(sin + ln.s1, L, prm, wmax, f, rc);
+            else if (!(exp_mask & 1)) match_read(sin + ln.s1, L, prm, wmax, f, rc);
             sel = f.k && rc.k;
             ReadResult o;
             o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : 0;
@@ -379,7 +379,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
 
     // ---- F: PrintSequence into the staging buffer (same 16-byte phase as the destination) --
     const uint32_t a0 = (uint32_t)(out_base & 15);
-    for (uint32_t j = tid; j < nproc; j += FT_THREADS) {
+    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += FT_THREADS) {
         const ReadResult rr = S.rec[j];
         if (rr.fck == 0) continue;
         const RecordLines ln = tile_record_lines(S.nl, (int)(i0 + 4 * j));
@@ -388,6 +388,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     __syncthreads();
 
     // ---- G: flush the staging buffer with aligned 16-byte stores ----------------------------
+    if (exp_mask & 8) return;
     uint8_t *dst = out + out_base;
     const uint32_t head = min(total, (16u - a0) & 15u);
     if (tid < head) dst[tid] = S.stage[a0 + tid];

@@ -37,6 +37,7 @@ struct bstr_ctx {
     bstr_params p;
     int dev;
     int sm_count;
+    int exp_mask;                  // BSTR_EXP: phase-skipping bits for profiling experiments
     bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
     cudaStream_t stream;
     cudaEvent_t ev[8];

@@ -241,43 +241,47 @@ __device__ __forceinline__ void revcomp_planes(Planes<W> &P, Bits<W> &nmask, int
     }
 }
 
-// Packed candidate key, compared as one unsigned 64-bit integer; mirrors the reference's
-// tuple order (len(STR), copies, STR/motif, start)  (select_STR_reads.pyx:93,101-102):
-//   bits 44..   len      bits 32..43 copies      bits 12..29 motif (6 x 3-bit symbols,
-//   first base most significant, left-aligned to 6 symbols is NOT needed: equal len and
-//   copies imply equal k)      bits 0..11 local start
-__device__ __forceinline__ uint64_t pack_key(int k, int c, uint32_t motif, int start)
+// ---------------------------------------------------------------------------------------
+// Joint two-strand scan.  For a period K let M(c) be the set of window positions s with at
+// least c copies of t[s:s+K] starting at s (M(c+1) = M(c) & M(c) >> K for c >= 2, M(2) = K
+// consecutive ones of E_K).  The regex is greedy, so a position counts for the copy number
+// c only if the repeat cannot be extended by one more copy:
+//   forward strand   start s:  c copies and s   not in M(c+1)          (extends rightwards)
+//   reverse strand   the same repeat read from its right end e = s + K*c; there the greedy
+//                    extension runs leftwards in forward coordinates:   s-K not in M(c+1)
+// and it is admissible iff s >= sh and s + K*c <= end_max on either strand (a greedy match
+// that violates a flank is DROPPED by the reference, never shortened: pyx:81-86).  Both
+// strands therefore come out of ONE pass over c with the same masks; the reverse
+// complement is never materialised.  The winner of the tuple order (len, copies, motif,
+// start) is the largest admissible c per period, the largest K*c over the periods, and
+// among the surviving positions a bit-parallel lexicographic filter on the motif symbols.
+// No data-dependent scalar candidate loops: every lane of a warp runs the same code.
+// ---------------------------------------------------------------------------------------
+template <int W> struct Best {
+    Bits<W> cand;      // positions (leftmost base of the repeat, window-local)
+    int k, c;          // k == 0: nothing admissible yet
+};
+
+// d = a << s (away from bit 0), s in [1,31]
+template <int W>
+__device__ __forceinline__ void shl(Bits<W> &d, const Bits<W> &a, int s)
 {
-    return ((uint64_t)(uint32_t)(k * c) << 44) | ((uint64_t)(uint32_t)c << 32) |
-           ((uint64_t)motif << 12) | (uint64_t)(uint32_t)start;
+#pragma unroll
+    for (int i = W - 1; i >= 0; i--)
+        d.w[i] = __funnelshift_l((i > 0) ? a.w[i - 1] : 0u, a.w[i], s);
 }
 
 template <int W>
-__device__ __forceinline__ uint32_t motif_key(const Planes<W> &P, int pos, int k)
+__device__ __forceinline__ void take_if_better(Best<W> &b, const Bits<W> &cand, int K, int c)
 {
-    const uint32_t b0 = extract32(P.p0, pos), b1 = extract32(P.p1, pos),
-                   b2 = ~extract32(P.p2, pos);
-    uint32_t key = 0;
-#pragma unroll
-    for (int j = 0; j < 6; j++)
-        if (j < k)
-            key = (key << 3) | (((b2 >> j) & 1u) << 2) | (((b1 >> j) & 1u) << 1) | ((b0 >> j) & 1u);
-    return key;
+    if (c && (K * c > b.k * b.c || (K * c == b.k * b.c && c > b.c))) { b.k = K; b.c = c; b.cand = cand; }
 }
 
-// State carried across the periods of one strand.
-template <int W> struct StrandState {
-    Bits<W> bcur;       // starts of the best (len, copies) class found so far
-    int bk, bc;         // its period and copy count (bk == 0: none)
-    uint64_t pbest;     // best fully evaluated candidate from partially admissible runs
-};
-
 template <int K, int W>
-__device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &nm,
-                                            const Bits<W> &hm, int sh, int end_max, int n,
-                                            bool use_hm, StrandState<W> &S)
+__device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &nm, const Bits<W> &hm,
+                                            bool use_hm, int sh, int end_max, int n,
+                                            Best<W> &bf, Best<W> &br)
 {
-    // local candidate start u must be >= sh, its greedy end must be <= end_max
     if (end_max - sh < K * n) return;
     Bits<W> E;
 #pragma unroll
@@ -287,113 +291,153 @@ __device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &n
         const uint32_t x2 = __funnelshift_r(P.p2.w[i], (i + 1 < W) ? P.p2.w[i + 1] : ~0u, K);
         E.w[i] = ~((P.p0.w[i] ^ x0) | (P.p1.w[i] ^ x1) | (P.p2.w[i] ^ x2));
     }
-    E.w[0] &= ~lowmask32(sh);                 // 5' flank: no start below sh
-    // A = starts with at least n copies = K(n-1) consecutive ones of E
-    Bits<W> A;
-    if (n <= 1) {
-        // one copy always matches as long as the motif itself fits; E cannot tell (it is
-        // zero where t[u+K] is past the window), so admit every start whose motif fits.
-        lowmask(A, end_max - K + 1);
-        A.w[0] &= ~lowmask32(sh);
-    } else {
+    // M2 = K consecutive ones of E = at least two copies
+    Bits<W> M2;
+    {
         Bits<W> t;
-        and_shr(t, E, E, 1);                                   // run >= 2
-        if (K == 2) A = t;
-        else if (K == 3) and_shr(A, t, E, 2);
-        else if (K == 4) and_shr(A, t, t, 2);
-        else if (K == 5) { Bits<W> u; and_shr(u, t, t, 2); and_shr(A, u, E, 4); }
-        else             { Bits<W> u; and_shr(u, t, t, 2); and_shr(A, u, t, 4); }
-        for (int c = 2; c < n; c++) { Bits<W> u = A; and_shr(A, u, u, K); }
+        and_shr(t, E, E, 1);
+        if (K == 2) M2 = t;
+        else if (K == 3) and_shr(M2, t, E, 2);
+        else if (K == 4) and_shr(M2, t, t, 2);
+        else if (K == 5) { Bits<W> u; and_shr(u, t, t, 2); and_shr(M2, u, E, 4); }
+        else             { Bits<W> u; and_shr(u, t, t, 2); and_shr(M2, u, t, 4); }
     }
+    // positions whose motif may be reported: no 'N' (pyx:76), not a homopolymer with -r (pyx:89).
+    // A repeat's copies are identical strings, so filtering M(c) up front equals filtering
+    // the candidates afterwards.
+    Bits<W> cur;
 #pragma unroll
     for (int i = 0; i < W; i++) {
-        A.w[i] &= ~nm.w[i];                                    // 'N' in motif (pyx:76)
-        if (use_hm) A.w[i] &= ~hm.w[i];                        // homopolymer motif (pyx:89)
+        uint32_t ok = ~nm.w[i];
+        if (use_hm) ok &= ~hm.w[i];
+        cur.w[i] = ok;
+        M2.w[i] &= ok;
     }
-    if (!A.any()) return;
-
-    // Runs that end at b <= p0 = end_max-K have every start admissible (greedy end b+K at
-    // most end_max).  a0 = start of the run covering p0 (or p0+1 if E[p0] == 0).
-    const int p0 = end_max - K;
-    Bits<W> Z;
-#pragma unroll
-    for (int i = 0; i < W; i++) Z.w[i] = ~E.w[i];
-    const int a0 = highest_set_le(Z, p0) + 1;
-    Bits<W> As;
-    {
-        Bits<W> m; lowmask(m, a0);
-#pragma unroll
-        for (int i = 0; i < W; i++) As.w[i] = A.w[i] & m.w[i];
+    Bits<W> lim;                                   // s + K*c <= end_max
+    int c = n <= 1 ? 1 : n;
+    lowmask(lim, end_max - K * c + 1);
+    lim.w[0] &= ~lowmask32(sh);                    // s >= sh (sh <= 6): folded into word 0 below
+    if (n <= 1) {
+        // c = 1: every position is a one-copy match; cur holds them (filtered)
+    } else {
+        cur = M2;
+        for (int cc = 2; cc < n; cc++) { Bits<W> u = cur; and_shr(cur, u, u, K); }
     }
-    if (a0 <= p0) {
-        // The run [a0, b0) covers p0.  A start i in it ends at the largest i + K*c <= b0+K;
-        // the reference drops it unless that end is <= end_max (pyx:84) -- it does not
-        // fall back to fewer copies.
-        Bits<W> m1; lowmask(m1, p0 + 1);
-        bool some = false;
+    int cf = 0, cr = 0;
+    Bits<W> df, dr;
 #pragma unroll
-        for (int i = 0; i < W; i++) some |= (A.w[i] & ~As.w[i] & m1.w[i]) != 0;
-        if (some) {
-            const int b0 = lowest_set_gt(Z, p0);
-            if (b0 < end_max) {
-                const int x = b0 + K - end_max;                // 1..K-1
+    for (int i = 0; i < W; i++) { df.w[i] = 0; dr.w[i] = 0; }
+    const uint32_t lo_keep = ~lowmask32(sh);
+    for (;;) {
+        if (!cur.any() || K * c > end_max - sh) break;
+        Bits<W> nxt, nl_;
+        if (c == 1) nxt = M2; else and_shr(nxt, cur, cur, K);
+        shl(nl_, nxt, K);
+        Bits<W> xf, xr;
+        uint32_t af = 0, ar = 0;
 #pragma unroll
-                for (int d = 0; d < K; d++) {
-                    const int i = a0 + d;
-                    if (i <= p0 && testbit(A, i)) {
-                        const int rr = b0 - i;
-                        if (rr % K >= x) {
-                            const uint64_t key = pack_key(K, 1 + rr / K, motif_key(P, i, K), i);
-                            if (key > S.pbest) S.pbest = key;
-                        }
-                    }
-                }
-            }
+        for (int i = 0; i < W; i++) {
+            const uint32_t l = lim.w[i];
+            xf.w[i] = cur.w[i] & ~nxt.w[i] & l;
+            xr.w[i] = cur.w[i] & ~nl_.w[i] & l;
+            af |= xf.w[i]; ar |= xr.w[i];
+        }
+        if (af) { cf = c; df = xf; }
+        if (ar) { cr = c; dr = xr; }
+        cur = nxt;
+        c++;
+        {   // lim for the next copy count: shift the upper bound down by K, keep s >= sh
+            Bits<W> u = lim;
+            shr(lim, u, K);
+            lim.w[0] &= lo_keep;
         }
     }
-    if (!As.any()) return;
-    // largest copy count among the fully admissible starts
-    int c = n;
-    Bits<W> cur = As;
-    bool more = true;
-    if (n <= 1) {
-        // As holds every start whose motif fits (one copy).  "One more copy" is K ones of E.
-        Bits<W> t, q;
-        and_shr(t, E, E, 1);
-        if (K == 2) q = t;
-        else if (K == 3) and_shr(q, t, E, 2);
-        else if (K == 4) and_shr(q, t, t, 2);
-        else if (K == 5) { Bits<W> u; and_shr(u, t, t, 2); and_shr(q, u, E, 4); }
-        else             { Bits<W> u; and_shr(u, t, t, 2); and_shr(q, u, t, 4); }
-        Bits<W> nx;
-#pragma unroll
-        for (int i = 0; i < W; i++) nx.w[i] = cur.w[i] & q.w[i];
-        if (nx.any()) { cur = nx; c = 2; } else more = false;
-    }
-    while (more) {
-        Bits<W> nx;
-        and_shr(nx, cur, cur, K);
-        if (!nx.any()) break;
-        cur = nx;
-        c++;
-    }
-    if (K * c > S.bk * S.bc || (K * c == S.bk * S.bc && c > S.bc)) {
-        S.bk = K; S.bc = c; S.bcur = cur;
-    }
+    take_if_better(bf, df, K, cf);
+    take_if_better(br, dr, K, cr);
 }
 
-// Best match of one strand given its planes.  Coordinates are window-local.
+// Forward winner among `cand` (all same k and copies): greatest motif bytes, then greatest
+// start (tuple order of pyx:93).  Symbol order '.' < A < C < G < T = (~p2, p1, p0).
 template <int W>
-__device__ __forceinline__ uint64_t strand_best(const Planes<W> &P, const Bits<W> &nmask,
-                                                int sh, int end_max, int n, int kmask,
-                                                bool use_hm)
+__device__ __forceinline__ int pick_forward(const Planes<W> &P, Bits<W> cand, int k)
 {
-    StrandState<W> S;
-    S.bk = 0; S.bc = 0; S.pbest = 0;
+    for (int j = 0; j < k; j++) {
+        Bits<W> x2, x1, x0;
+        if (j) { shr(x2, P.p2, j, ~0u); shr(x1, P.p1, j, ~0u); shr(x0, P.p0, j); }
+        else { x2 = P.p2; x1 = P.p1; x0 = P.p0; }
+        Bits<W> t;
 #pragma unroll
-    for (int i = 0; i < W; i++) S.bcur.w[i] = 0;
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & ~x2.w[i];
+        if (t.any()) cand = t;
+#pragma unroll
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & x1.w[i];
+        if (t.any()) cand = t;
+#pragma unroll
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & x0.w[i];
+        if (t.any()) cand = t;
+    }
+    return highest_set_le(cand, 32 * W - 1);
+}
 
-    // nm_k = starts whose k-window holds an N; hm_k = starts whose k-window is one symbol
+// Reverse-strand winner: the reported motif is revcomp(t[s:s+k]), compared from its first
+// base = complement of t[s+k-1]; complement reverses A<C<G<T and leaves '.' lowest.  Then
+// the greatest reverse-strand start = the smallest forward position.
+template <int W>
+__device__ __forceinline__ int pick_reverse(const Planes<W> &P, Bits<W> cand, int k)
+{
+    for (int j = k - 1; j >= 0; j--) {
+        Bits<W> x2, x1, x0;
+        if (j) { shr(x2, P.p2, j, ~0u); shr(x1, P.p1, j, ~0u); shr(x0, P.p0, j); }
+        else { x2 = P.p2; x1 = P.p1; x0 = P.p0; }
+        Bits<W> t;
+#pragma unroll
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & ~x2.w[i];
+        if (t.any()) cand = t;
+#pragma unroll
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & ~x1.w[i];
+        if (t.any()) cand = t;
+#pragma unroll
+        for (int i = 0; i < W; i++) t.w[i] = cand.w[i] & ~x0.w[i];
+        if (t.any()) cand = t;
+    }
+    return lowest_set_gt(cand, -1);
+}
+
+// all k symbols at pos equal?  (IsHomopolymer, pyx:51-56)
+template <int W>
+__device__ __forceinline__ bool motif_is_homopolymer(const Planes<W> &P, int pos, int k)
+{
+    const uint32_t m = (1u << k) - 1u;
+    const uint32_t a = extract32(P.p0, pos) & m, b = extract32(P.p1, pos) & m, c = extract32(P.p2, pos) & m;
+    return (a == 0 || a == m) && (b == 0 || b == m) && (c == 0 || c == m);
+}
+
+// Both strands of one read with a W-word window.  seq = first base, L = read length.
+template <int W>
+__device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const ScanParams &prm,
+                                                Hit &fwd, Hit &rc)
+{
+    fwd.k = 0; rc.k = 0; fwd.copies = rc.copies = fwd.start = rc.start = 0;
+    const int fe = prm.altalgo ? prm.f : 0;          // -x: candidates ignore the flanks
+    const int g0 = fe > 6 ? fe - 6 : 0;              // window = [g0, L - g0)
+    const int Gn = L - 2 * g0;
+    const int sh = fe - g0;
+    const int end_max = sh + (L - 2 * fe);           // local bound on a candidate's end
+    const int n = prm.n < 1 ? 1 : prm.n;
+    if (Gn <= 0 || end_max - sh < 2 * n) return;
+    const bool use_hm = prm.altalgo && prm.rmhm;
+
+    Planes<W> P;
+    Bits<W> nmask;
+    encode_window<W>(seq + g0, Gn, P, nmask);
+    mark_invalid(P, Gn);
+
+    Best<W> bf, br;
+    bf.k = bf.c = br.k = br.c = 0;
+#pragma unroll
+    for (int i = 0; i < W; i++) { bf.cand.w[i] = 0; br.cand.w[i] = 0; }
+
+    // nm_k = positions whose k-window holds an N; hm_k = positions whose k-window is one symbol
     Bits<W> nm = nmask, hm, E1;
     if (use_hm) {
 #pragma unroll
@@ -414,89 +458,31 @@ __device__ __forceinline__ uint64_t strand_best(const Planes<W> &P, const Bits<W
         shr(t_, nmask, (K) - 1);                                                    \
         _Pragma("unroll") for (int i = 0; i < W; i++) nm.w[i] |= t_.w[i];           \
         if (use_hm && (K) > 2) { Bits<W> h_ = hm; and_shr(hm, h_, E1, (K) - 2); }   \
-        if (kmask & (1 << (K))) scan_period<K, W>(P, nm, hm, sh, end_max, n, use_hm, S); \
+        if (prm.kmask & (1 << (K))) scan_period<K, W>(P, nm, hm, use_hm, sh, end_max, n, bf, br); \
     }
     BSTR_PERIOD(2) BSTR_PERIOD(3) BSTR_PERIOD(4) BSTR_PERIOD(5) BSTR_PERIOD(6)
 #undef BSTR_PERIOD
 
-    uint64_t best = S.pbest;
-    if (S.bk) {
-        // every set bit of bcur is a start with exactly bc copies of period bk; the tuple
-        // order then prefers the greatest motif bytes, then the greatest start.
-#pragma unroll
-        for (int i = W - 1; i >= 0; i--) {
-            uint32_t v = S.bcur.w[i];
-            while (v) {
-                const int pos = 32 * i + 31 - __clz(v);
-                v &= ~(1u << (pos & 31));
-                const uint64_t key = pack_key(S.bk, S.bc, motif_key(P, pos, S.bk), pos);
-                if (key > best) best = key;
-            }
+    if (bf.k == 0) return;                           // ProcessSequence: forward None -> drop
+    {
+        const int pos = pick_forward(P, bf.cand, bf.k);
+        const int start = g0 + pos, len = bf.k * bf.c;
+        if (!prm.altalgo) {                          // -x: tests on the winner only (pyx:153-167)
+            if (start < prm.f || L - (start + len) < prm.f) return;
+            if (prm.rmhm && motif_is_homopolymer(P, pos, bf.k)) return;
         }
+        fwd.k = bf.k; fwd.copies = bf.c; fwd.start = start;
     }
-    return best;
-}
-
-__device__ __forceinline__ Hit unpack_hit(uint64_t key, int base)
-{
-    Hit h;
-    if (key == 0) { h.k = 0; h.copies = 0; h.start = 0; return h; }
-    const int len = (int)(key >> 44), c = (int)((key >> 32) & 0xFFF);
-    h.copies = c; h.k = len / c; h.start = base + (int)(key & 0xFFF);
-    return h;
-}
-
-// -x: flank and homopolymer tests apply to the winner only (select_STR_reads.pyx:153-167)
-template <int W>
-__device__ __forceinline__ uint64_t xalgo_filter(uint64_t key, const ScanParams &prm, int L)
-{
-    if (key == 0) return 0;
-    const int len = (int)(key >> 44), c = (int)((key >> 32) & 0xFFF), start = (int)(key & 0xFFF);
-    const int k = len / c;
-    if (start < prm.f || L - (start + len) < prm.f) return 0;
-    if (prm.rmhm) {
-        const uint32_t m = (uint32_t)(key >> 12) & 0x3FFFF;
-        bool same = true;
-        for (int j = 1; j < k; j++) same &= ((m >> (3 * j)) & 7u) == (m & 7u);
-        if (same) return 0;
+    if (br.k == 0) return;
+    {
+        const int pos = pick_reverse(P, br.cand, br.k);
+        const int len = br.k * br.c, rstart = L - (g0 + pos + len);
+        if (!prm.altalgo) {
+            if (rstart < prm.f || g0 + pos < prm.f) return;
+            if (prm.rmhm && motif_is_homopolymer(P, pos, br.k)) return;
+        }
+        rc.k = br.k; rc.copies = br.c; rc.start = rstart;
     }
-    return key;
-}
-
-// Both strands of one read with a W-word window.  seq = first base, L = read length.
-template <int W>
-__device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const ScanParams &prm,
-                                                Hit &fwd, Hit &rc)
-{
-    fwd.k = 0; rc.k = 0; fwd.copies = rc.copies = fwd.start = rc.start = 0;
-    const int fe = prm.altalgo ? prm.f : 0;          // -x: candidates ignore the flanks
-    const int g0 = fe > 6 ? fe - 6 : 0;              // window = [g0, L - g0)
-    const int Gn = L - 2 * g0;
-    const int sh = fe - g0;
-    const int end_max = sh + (L - 2 * fe);           // local bound on a candidate's end
-    const int n = prm.n < 1 ? 1 : prm.n;
-    if (Gn <= 0 || end_max - sh < 2 * n) return;
-    const bool use_hm = prm.altalgo && prm.rmhm;
-
-    Planes<W> raw;
-    Bits<W> rawn;
-    encode_window<W>(seq + g0, Gn, raw, rawn);
-    uint64_t key0 = 0, key1 = 0;
-    // one copy of the strand code, run twice (keeps the kernel inside the instruction cache)
-#pragma unroll 1
-    for (int strand = 0; strand < 2; strand++) {
-        Planes<W> Q = raw;
-        Bits<W> qn = rawn;
-        if (strand) revcomp_planes(Q, qn, Gn);       // ReverseComplement, pyx:187-189
-        mark_invalid(Q, Gn);
-        uint64_t k = strand_best<W>(Q, qn, sh, end_max, n, prm.kmask, use_hm);
-        if (!prm.altalgo) k = xalgo_filter<W>(k, prm, L);
-        if (strand) key1 = k; else key0 = k;
-        if (k == 0) break;                           // ProcessSequence: a strand with None drops the read
-    }
-    if (key0 == 0) return;
-    fwd = unpack_hit(key0, g0);
-    rc = unpack_hit(key1, g0);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -130,7 +130,7 @@ static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final
     if (n_tiles)
         k_fused_tile<<<n_tiles, FT_THREADS, sizeof(FusedShared), st>>>(
             s.d_in, nbytes, final, prm, ctx->p.illumina_quals, s.d_state, lb_lines, lb_out, ticket,
-            n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out);
+            n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out, ctx->exp_mask);
     if (ev) { cudaEventRecord(ev[2], st); cudaEventRecord(ev[4], st); }
     CUDA_TRY(cudaGetLastError());
     return BSTR_OK;
@@ -226,6 +226,8 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     {
         const char *fg = getenv("BSTR_FORCE_GENERIC");
         ctx->force_generic = fg && fg[0] == '1';
+        const char *ex = getenv("BSTR_EXP");           // profiling experiments only: skips phases
+        ctx->exp_mask = ex ? atoi(ex) : 0;
     }
     e = cudaFuncSetAttribute(k_fused_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FusedShared));
     if (e != cudaSuccess) {
