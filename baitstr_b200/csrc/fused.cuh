@@ -1,6 +1,6 @@
 // fused.cuh -- the single-pass tile kernel of the select stage (sm_100a).
 //
-// One CTA owns FT_TILE bytes of raw FASTQ (plus FT_OVL bytes of look-ahead for the records
+// One CTA owns TileGeom::tile bytes of raw FASTQ (plus FT_OVL bytes of look-ahead for the records
 // that start in its tile) staged in shared memory, and does everything the reference does
 // per record in one visit of the data:
 //   fastq.next()            /root/reference/src/fastq.pyx:72-94            (line split, checks)
@@ -11,7 +11,7 @@
 // byte written once.  Tiles are chained by two decoupled look-backs (line count, output
 // bytes), tickets are handed out in launch order so a tile only ever waits for tiles that
 // already run.  Inputs the tile geometry cannot hold (records longer than FT_OVL, more
-// than FT_NLMAX lines in a tile, ...) raise BatchState::fallback and the host re-runs the
+// lines or records than the tile's tables hold, ...) raise BatchState::fallback and the host re-runs the
 // batch through the staged generic kernels (kernels_v1.cuh) -- still on the GPU.
 #pragma once
 #include <stdint.h>
@@ -19,33 +19,57 @@
 
 namespace bstr {
 
-constexpr int FT_THREADS = 256;
-constexpr int FT_TILE = 32768;                 // bytes owned by one tile
+constexpr int FT_MAXTHREADS = 256;            // launch bound; the host picks 64..256 per batch
+constexpr int FT_MAXCPT = 16;                  // 16-byte chunks per thread in the index phase
 constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
-constexpr int FT_REGION = FT_TILE + FT_OVL;
-constexpr int FT_CHUNKS = FT_REGION / 16;      // 16-byte chunks in the staged region
-constexpr int FT_CPT = FT_CHUNKS / FT_THREADS; // chunks per thread (contiguous)
-constexpr int FT_NLMAX = 2048;                 // line table entries
-constexpr int FT_RECMAX = 512;                 // records per tile
-constexpr int FT_STAGE = 40960;                // output staging bytes
-static_assert(FT_CHUNKS % FT_THREADS == 0, "region must split evenly over the threads");
-static_assert(FT_RECMAX == 2 * FT_THREADS, "offset scan assumes two records per thread");
+constexpr int FT_MAXREGION = 65504;            // line positions are 16-bit
+constexpr int FT_MINTILE = 8192;
+constexpr int FT_DEFTILE = 40960;
+constexpr int FT_MAXSMEM = 200 * 1024;         // opt-in dynamic shared memory limit of the kernel
 
 constexpr unsigned long long LB_MASK = (1ull << 62) - 1;
 constexpr unsigned long long LB_AGG = 1ull << 62;      // tile aggregate published
 constexpr unsigned long long LB_INC = 2ull << 62;      // inclusive prefix published
 
-struct FusedShared {
-    alignas(16) uint8_t in_raw[16 + FT_REGION + 32];    // tile bytes at in_raw + 16
-    alignas(16) uint8_t stage[FT_STAGE + 32];
-    uint16_t nl[FT_NLMAX + 8];                          // newline position + 1 (tile-relative)
-    ReadResult rec[FT_RECMAX];
-    uint32_t outoff[FT_RECMAX];                         // outlen, then exclusive offsets
-    uint32_t warp_tmp[FT_THREADS / 32];
+// Tile geometry, chosen by the host per batch from the average record size (select_host.cu:
+// pick_geometry) so that a tile holds about as many records as the CTA has threads: the
+// per-record phases (validate, match, format) then run with full warps and no warp idles
+// at the barriers between the phases.
+struct TileGeom {
+    uint32_t threads;        // CTA size, multiple of 32
+    uint32_t tile;           // bytes owned by one tile (multiple of 16)
+    uint32_t region;         // tile + FT_OVL
+    uint32_t chunks;         // region / 16
+    uint32_t cpt;            // chunks per thread (contiguous), <= FT_MAXCPT
+    uint32_t recmax;         // 2 * threads: records a tile may own
+    uint32_t nlmax;          // line-table entries
+    uint32_t stage;          // output staging bytes
+    uint32_t off_in, off_stage, off_rec, off_outoff, off_nl;   // byte offsets in dynamic smem
+    uint32_t smem_bytes;
+};
+
+struct FusedVars {                                      // at offset 0 of the dynamic smem
     long long gbase;                                    // global index of local line 0
     unsigned long long out_base;
-    uint32_t tile, cnt_own, cnt_all, total_out, bail;
+    uint32_t tile, pad0;
+    uint32_t warp_tmp[FT_MAXTHREADS / 32];
 };
+
+inline TileGeom make_geometry(uint32_t tile, uint32_t threads, uint32_t stage)
+{
+    TileGeom g;
+    g.threads = threads; g.tile = tile; g.region = tile + FT_OVL; g.chunks = g.region / 16;
+    g.cpt = (g.chunks + threads - 1) / threads;
+    g.recmax = 2 * threads; g.nlmax = 5 * g.recmax + 64; g.stage = stage;
+    uint32_t o = (sizeof(FusedVars) + 15) & ~15u;
+    g.off_in = o;       o += 16 + g.region + 32;
+    g.off_stage = o;    o += g.stage + 32;
+    g.off_rec = o;      o += g.recmax * 16;
+    g.off_outoff = o;   o += g.recmax * 4;
+    g.off_nl = o;       o += (g.nlmax + 8) * 2;
+    g.smem_bytes = (o + 15) & ~15u;
+    return g;
+}
 
 // Decoupled look-back, run by one full warp.  st[] was zeroed before the launch.  Returns
 // the exclusive prefix of `agg` over the tiles before `tile`.
@@ -92,7 +116,7 @@ __device__ __forceinline__ uint32_t nl_mask_of(const uint4 v)
 // exclusive scan of one value per thread over the CTA; *total gets the sum
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_tmp, uint32_t *total)
 {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     uint32_t inc = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -104,8 +128,8 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_t
     __syncthreads();
     uint32_t wbase = 0, tot = 0;
 #pragma unroll
-    for (int w = 0; w < FT_THREADS / 32; w++) {
-        const uint32_t x = warp_tmp[w];
+    for (int w = 0; w < FT_MAXTHREADS / 32; w++) {
+        const uint32_t x = w < nw ? warp_tmp[w] : 0u;
         if (w < wid) wbase += x;
         tot += x;
     }
@@ -195,79 +219,114 @@ __device__ __forceinline__ void format_record_words(const uint8_t *in, const Rec
     *p++ = '\n';
 }
 
-__global__ void __launch_bounds__(FT_THREADS, 2)
+// Line index of this thread's chunks: packs the 16-bit newline masks of up to FT_MAXCPT
+// chunks into mk[] and returns (newlines in the window) << 16 | (newlines in the owned tile).
+// CAREFUL = the window reaches the end of the batch: bytes past n are masked and, on the
+// final batch, an unterminated last line gets its virtual newline.
+template <bool CAREFUL>
+__device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileGeom &g, uint32_t c0,
+                                                 uint64_t ts, uint64_t n, int final, uint64_t (&mk)[FT_MAXCPT / 4])
+{
+    uint32_t cnt = 0;
+    const uint32_t own = g.tile / 16;
+#pragma unroll
+    for (int i = 0; i < FT_MAXCPT; i++) {
+        if (i < (int)g.cpt) {
+            const uint32_t c = c0 + i;
+            uint32_t m = 0;
+            if (c < g.chunks) {
+                if (!CAREFUL) {
+                    m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
+                } else {
+                    const uint64_t gpos = ts + 16ull * c;
+                    if (gpos < n) {
+                        m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
+                        const uint64_t rem = n - gpos;
+                        if (rem < 16) m &= (1u << rem) - 1u;
+                        // an unterminated last line: its last byte is dropped by line[:-1]
+                        // (fastq.pyx:78,83,90), i.e. it plays the newline
+                        if (final && rem <= 16) m |= 1u << (rem - 1);
+                    }
+                }
+            }
+            mk[i >> 2] |= (uint64_t)m << (16 * (i & 3));
+            const uint32_t pc = __popc(m);
+            cnt += (pc << 16) | (c < own ? pc : 0u);
+        }
+    }
+    return cnt;
+}
+
+__global__ void __launch_bounds__(FT_MAXTHREADS, 2)
 k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
              BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
              unsigned long long *ticket, uint32_t ntiles, ReadResult *res, uint8_t *out,
-             uint64_t outcap, int exp_mask)
+             uint64_t outcap, int exp_mask, const TileGeom g)
 {
     extern __shared__ __align__(16) uint8_t fused_smem[];
-    FusedShared &S = *reinterpret_cast<FusedShared *>(fused_smem);
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    FusedVars &S = *reinterpret_cast<FusedVars *>(fused_smem);
+    uint8_t *const in_raw = fused_smem + g.off_in;
+    uint8_t *const sin = in_raw + 16;                        // tile bytes; 16 B of zero slack before
+    uint8_t *const stage = fused_smem + g.off_stage;
+    ReadResult *const s_rec = reinterpret_cast<ReadResult *>(fused_smem + g.off_rec);
+    uint32_t *const s_outoff = reinterpret_cast<uint32_t *>(fused_smem + g.off_outoff);
+    uint16_t *const s_nl = reinterpret_cast<uint16_t *>(fused_smem + g.off_nl);   // newline position + 1
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nthr = blockDim.x;
     if (tid == 0) S.tile = (uint32_t)atomicAdd(ticket, 1ull);
     if (tid < 4) {
-        reinterpret_cast<uint32_t *>(S.in_raw)[tid] = 0u;
-        reinterpret_cast<uint32_t *>(S.in_raw + 16 + FT_REGION)[tid] = 0u;
-        reinterpret_cast<uint32_t *>(S.in_raw + 16 + FT_REGION + 16)[tid] = 0u;
+        reinterpret_cast<uint32_t *>(in_raw)[tid] = 0u;
+        reinterpret_cast<uint32_t *>(sin + g.region)[tid] = 0u;
+        reinterpret_cast<uint32_t *>(sin + g.region + 16)[tid] = 0u;
     }
     __syncthreads();
     const uint32_t tile = S.tile;
-    const uint64_t ts = (uint64_t)tile * FT_TILE;
-    uint8_t *sin = S.in_raw + 16;
-    const bool reach = ts + FT_REGION >= n;          // the staged window covers the batch end
+    const uint64_t ts = (uint64_t)tile * g.tile;
+    const bool reach = ts + g.region >= n;           // the staged window covers the batch end
     const bool last = tile == ntiles - 1;
 
     // ---- A: stage the tile (+ look-ahead) in shared memory, 16-byte coalesced loads -------
+    for (uint32_t cb = 0; cb < g.chunks; cb += 4 * nthr) {
+        uint4 v[4];
 #pragma unroll
-    for (int i = 0; i < FT_CPT; i++) {
-        const int c = i * FT_THREADS + tid;
-        const uint64_t off = ts + 16ull * c;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (off < n) v = __ldg(reinterpret_cast<const uint4 *>(in + off));
-        *reinterpret_cast<uint4 *>(sin + 16 * c) = v;
+        for (int u = 0; u < 4; u++) {
+            const uint32_t c = cb + u * nthr + tid;
+            const uint64_t off = ts + 16ull * c;
+            v[u] = make_uint4(0, 0, 0, 0);
+            if (c < g.chunks && off < n) v[u] = __ldg(reinterpret_cast<const uint4 *>(in + off));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t c = cb + u * nthr + tid;
+            if (c < g.chunks) *reinterpret_cast<uint4 *>(sin + 16 * c) = v[u];
+        }
     }
     __syncthreads();
 
     // ---- B: line index of the window -----------------------------------------------------
-    uint32_t masks[FT_CPT];
-    uint32_t cnt = 0;                                // all << 16 | own
-#pragma unroll
-    for (int i = 0; i < FT_CPT; i++) {
-        const int c = tid * FT_CPT + i;
-        const uint64_t gpos = ts + 16ull * c;
-        uint32_t m = 0;
-        if (gpos < n) {
-            m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
-            const uint64_t rem = n - gpos;
-            if (rem < 16) m &= (1u << rem) - 1u;
-            // an unterminated last line: its last byte is dropped by line[:-1]
-            // (fastq.pyx:78,83,90), i.e. it plays the newline
-            if (final && rem <= 16) m |= 1u << (rem - 1);
-        }
-        masks[i] = m;
-        const uint32_t pc = __popc(m);
-        cnt += (pc << 16) | (c < FT_TILE / 16 ? pc : 0u);
-    }
+    uint64_t mk[FT_MAXCPT / 4] = {0, 0, 0, 0};
+    const uint32_t c0 = tid * g.cpt;
+    const uint32_t cnt = reach ? index_chunks<true>(sin, g, c0, ts, n, final, mk)
+                               : index_chunks<false>(sin, g, c0, ts, n, final, mk);   // all << 16 | own
     uint32_t tot;
     const uint32_t ex = block_excl_scan(cnt, S.warp_tmp, &tot);
     const uint32_t shift = tile == 0 ? 1u : 0u;      // tile 0: virtual newline before byte 0
     const uint32_t real_own = tot & 0xFFFFu;
     uint32_t cnt_own = real_own + shift, cnt_all = (tot >> 16) + shift;
-    bool bail = cnt_all + 2 > FT_NLMAX;
+    bool bail = cnt_all + 2 > g.nlmax;
     {
         uint32_t idx = (ex >> 16) + shift;
 #pragma unroll
-        for (int i = 0; i < FT_CPT; i++) {
-            uint32_t m = masks[i];
-            const uint32_t base = 16u * (tid * FT_CPT + i) + 1u;
+        for (int w = 0; w < FT_MAXCPT / 4; w++) {
+            uint64_t m = mk[w];
+            const uint32_t base = 16u * (c0 + 4 * w) + 1u;
             while (m) {
-                const int b = __ffs(m) - 1;
+                const int b = __ffsll((long long)m) - 1;
                 m &= m - 1;
-                if (idx < FT_NLMAX) S.nl[idx] = (uint16_t)(base + b);
+                if (idx < g.nlmax) s_nl[idx] = (uint16_t)(base + b);
                 idx++;
             }
         }
-        if (tid == 0 && shift) S.nl[0] = 0;
+        if (tid == 0 && shift) s_nl[0] = 0;
     }
 
     // ---- C: global line number of the tile's first line (look-back #1) ---------------------
@@ -281,7 +340,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     if (final && reach && (G & 3) == 3 && !bail) {
         // EOF after the separator line: accepted with an empty quality string
         // (readline() returns '' at fastq.pyx:89)
-        if (tid == 0) S.nl[cnt_all] = (uint16_t)(n - ts + 1);
+        if (tid == 0) s_nl[cnt_all] = (uint16_t)(n - ts + 1);
         cnt_all++;
     }
     if (last && tid == 0) {
@@ -299,10 +358,10 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     uint32_t nproc = cnt_all >= i0 + 5 ? (cnt_all - 1 - i0) / 4 : 0u;
     if (nproc > nrec_own) nproc = nrec_own;
     if (nproc < nrec_own && !reach) bail = true;      // a record runs past the look-ahead
-    if (nproc > FT_RECMAX) bail = true;
+    if (nproc > g.recmax) bail = true;
     if (!bail && nrec_own && tid == 0) {
         const uint32_t iL = i0 + 4 * (nrec_own - 1);
-        if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + S.nl[iL]);
+        if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + s_nl[iL]);
     }
     if (!bail && final && reach && nproc < nrec_own && tid == 0) {
         // a record cut short by EOF: the reference still tests its header (fastq.pyx:77) and a
@@ -310,26 +369,26 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
         const uint32_t i = i0 + 4 * nproc, after = cnt_all - 1 - i;
         if (after >= 1) {
             const unsigned long long r = (unsigned long long)(G >> 2);
-            if (sin[S.nl[i]] != '@') atomicMin(&st->first_bad, (r << 8) | BAD_HEADER);
-            else if (after >= 2 && bases_invalid(sin + S.nl[i + 1], (int)S.nl[i + 2] - 1 - (int)S.nl[i + 1]))
+            if (sin[s_nl[i]] != '@') atomicMin(&st->first_bad, (r << 8) | BAD_HEADER);
+            else if (after >= 2 && bases_invalid(sin + s_nl[i + 1], (int)s_nl[i + 2] - 1 - (int)s_nl[i + 1]))
                 atomicMin(&st->first_bad, (r << 8) | BAD_BASES);
         }
     }
     if (bail) nproc = 0;
-    __syncthreads();                                  // S.nl complete (virtual entry included)
+    __syncthreads();                                  // s_nl complete (virtual entry included)
 
     // ---- D: per record: fastq.next() checks + both-strand match (thread per record) --------
     uint32_t nsel = 0;
-    for (uint32_t jb = 0; jb < FT_RECMAX; jb += FT_THREADS) {
+    for (uint32_t jb = 0; jb < g.recmax; jb += nthr) {
         const uint32_t j = jb + tid;
         const bool live = j < nproc;
         if (jb >= nproc) {                            // CTA-uniform: nothing left in this round
-            S.outoff[j] = 0;
+            s_outoff[j] = 0;
             continue;
         }
         RecordLines ln = {};
         int L = 0;
-        if (live) { ln = tile_record_lines(S.nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
+        if (live) { ln = tile_record_lines(s_nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
         const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
         Hit f, rc;
         f.k = rc.k = 0; f.copies = rc.copies = f.start = rc.start = 0;
@@ -348,22 +407,22 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
             o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : 0;
             o.fck = sel ? ((uint32_t)f.copies << 3 | f.k) : 0;
             o.rck = sel ? ((uint32_t)rc.copies << 3 | rc.k) : 0;
-            S.rec[j] = o;
+            s_rec[j] = o;
             if (res) res[r] = o;
             if (sel) olen = record_out_len(ln.e0 - ln.s0 - 1, L, ln.e3 - ln.s3, f, rc);
         }
-        S.outoff[j] = olen;
+        s_outoff[j] = olen;
         nsel += __popc(__ballot_sync(0xFFFFFFFFu, sel));
     }
     __syncthreads();
 
     // ---- E: output offsets: records inside the tile, then the tile (look-back #2) ---------
-    const uint32_t o0 = S.outoff[2 * tid], o1 = S.outoff[2 * tid + 1];
+    const uint32_t o0 = s_outoff[2 * tid], o1 = s_outoff[2 * tid + 1];
     uint32_t total;
     const uint32_t oex = block_excl_scan(o0 + o1, S.warp_tmp, &total);
-    S.outoff[2 * tid] = oex;
-    S.outoff[2 * tid + 1] = oex + o0;
-    if (total > FT_STAGE - 16) { bail = true; total = 0; nproc = 0; }
+    s_outoff[2 * tid] = oex;
+    s_outoff[2 * tid + 1] = oex + o0;
+    if (total > g.stage - 16) { bail = true; total = 0; nproc = 0; }
     if (bail && tid == 0) atomicExch(&st->fallback, 1ull);
     if (wid == 0) {
         const unsigned long long ob = warp_lookback(lb_out, (int)tile, total);
@@ -379,11 +438,11 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
 
     // ---- F: PrintSequence into the staging buffer (same 16-byte phase as the destination) --
     const uint32_t a0 = (uint32_t)(out_base & 15);
-    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += FT_THREADS) {
-        const ReadResult rr = S.rec[j];
+    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += nthr) {
+        const ReadResult rr = s_rec[j];
         if (rr.fck == 0) continue;
-        const RecordLines ln = tile_record_lines(S.nl, (int)(i0 + 4 * j));
-        format_record_words(sin, ln, rr, illumina, S.stage + a0 + S.outoff[j]);
+        const RecordLines ln = tile_record_lines(s_nl, (int)(i0 + 4 * j));
+        format_record_words(sin, ln, rr, illumina, stage + a0 + s_outoff[j]);
     }
     __syncthreads();
 
@@ -391,13 +450,13 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     if (exp_mask & 8) return;
     uint8_t *dst = out + out_base;
     const uint32_t head = min(total, (16u - a0) & 15u);
-    if (tid < head) dst[tid] = S.stage[a0 + tid];
+    if (tid < head) dst[tid] = stage[a0 + tid];
     const uint32_t nchunk = (total - head) >> 4;
-    const uint8_t *sb = S.stage + a0 + head;
-    for (uint32_t c = tid; c < nchunk; c += FT_THREADS)
+    const uint8_t *sb = stage + a0 + head;
+    for (uint32_t c = tid; c < nchunk; c += nthr)
         *reinterpret_cast<uint4 *>(dst + head + 16 * c) = *reinterpret_cast<const uint4 *>(sb + 16 * c);
     const uint32_t done = head + (nchunk << 4);
-    if (tid < total - done) dst[done + tid] = S.stage[a0 + done + tid];
+    if (tid < total - done) dst[done + tid] = stage[a0 + done + tid];
 }
 
 }  // namespace bstr

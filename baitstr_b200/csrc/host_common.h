@@ -25,6 +25,7 @@ struct DeviceSlot {
     BatchState *d_state, *h_state;
     uint8_t *h_out;                // pinned
     ReadResult *h_res;             // pinned
+    double rec_bytes;              // average record size of the batch in d_in (tile geometry)
     size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres, cap_lb;
 
     int reserve(struct ::bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need);
@@ -38,6 +39,10 @@ struct bstr_ctx {
     int dev;
     int sm_count;
     int exp_mask;                  // BSTR_EXP: phase-skipping bits for profiling experiments
+    uint32_t geom_tile, geom_threads, geom_stage;   // BSTR_GEOM overrides (0 = automatic)
+    uint32_t wgeom_tile, wgeom_ovl, wgeom_stage;    // BSTR_WGEOM overrides (0 = automatic)
+    double wgeom_recs;             // records per warp tile
+    bool use_cta_kernel;           // default; BSTR_KERNEL=warp selects k_fused_warp
     bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
     cudaStream_t stream;
     cudaEvent_t ev[8];
@@ -60,6 +65,7 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
                     cudaEvent_t *ev, bool generic = false);
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record);
 void stream_release(bstr_ctx *ctx);
+double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes);
 int pipeline_stage_count(const bstr_ctx *ctx);
 const char *pipeline_stage_name(const bstr_ctx *ctx, int k);
 int pipeline_launches_per_batch(const bstr_ctx *ctx);

@@ -32,6 +32,15 @@ CFG, READ_LEN = 2, 100
 READS_PER_GPU = 10_000_000
 BATCH_READS = 1_000_000
 FLAGS = dict(n=2, f=31, ks=None, rmhm=False, altalgo=True, illumina=False)
+WORKLOAD = ("C2: synthetic 10M paired 100bp reads with planted 2-6mer STRs, "
+            "default flags (-n 2 -f 31, 2-6mers), per GPU")
+# the other BASELINE.json configs, for sweeps (--workload); the bench line of record is C2
+WORKLOADS = {
+    "C2": (2, 100, dict(FLAGS), WORKLOAD),
+    "C3": (3, 150, dict(FLAGS, n=3, rmhm=True), "C3: synthetic 150bp reads, -n 3 -r, per GPU"),
+    "C4": (4, 250, dict(FLAGS, ks=[2, 3], f=41), "C4: synthetic 250bp reads, --2mer --3mer -f 41, per GPU"),
+    "C5": (5, 150, dict(FLAGS), "C5: synthetic 150bp reads, default flags, per GPU"),
+}
 METRIC = "reads/s scanned (select_STR_reads hot path: parse+scan+compact+format)"
 
 
@@ -216,8 +225,7 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": "C2: synthetic 10M paired 100bp reads with planted 2-6mer STRs, "
-                               "default flags (-n 2 -f 31, 2-6mers), per GPU",
+        "config": {"workload": WORKLOAD,
                    "reads_per_gpu": nreads, "read_len": READ_LEN, "batch_reads": args.batch_reads,
                    "raw_fastq_bytes_per_gpu": in_bytes, "selected_fraction": round(sel_frac, 4),
                    "l2_policy": "inputs larger than L2 (%.2f GB read per step), no flush" % (in_bytes / 1e9),
@@ -282,8 +290,7 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(total / args.steps * 1e3, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2: synthetic 10M paired 100bp reads with planted 2-6mer STRs, "
-                               "default flags (-n 2 -f 31, 2-6mers), per GPU",
+        "config": {"workload": WORKLOAD,
                    "read_len": READ_LEN,
                    "note": "each step = the first %d reads of the workload (prefix), files in tmpfs, "
                            "stdout to /dev/null; interpreter CPython %d.%d + Cython shim build "
@@ -308,7 +315,10 @@ def main():
     ap.add_argument("--batch-reads", type=int, default=BATCH_READS)
     ap.add_argument("--cpu-sample", type=int, default=1_000_000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     args = ap.parse_args()
+    global CFG, READ_LEN, FLAGS, WORKLOAD
+    CFG, READ_LEN, FLAGS, WORKLOAD = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
         run_reference(args)
