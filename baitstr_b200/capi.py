@@ -48,7 +48,8 @@ class BenchOut(C.Structure):
 
 EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "bstr_scan_batch",
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
-           "bstr_get_stats", "bstr_reset_stats", "bstr_device_count"]
+           "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
+           "bstr_submit_batch", "bstr_collect_batch"]
 
 _lib = None
 
@@ -79,6 +80,12 @@ def load_library():
     lib.bstr_run_files.restype = C.c_int
     lib.bstr_scan_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(BatchOut)]
     lib.bstr_scan_batch.restype = C.c_int
+    lib.bstr_lanes.argtypes = [C.c_void_p]
+    lib.bstr_lanes.restype = C.c_int
+    lib.bstr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_int]
+    lib.bstr_submit_batch.restype = C.c_int
+    lib.bstr_collect_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(BatchOut)]
+    lib.bstr_collect_batch.restype = C.c_int
     lib.bstr_match_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.bstr_match_reads.restype = C.c_int
     lib.bstr_bench_resident.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
@@ -214,6 +221,34 @@ class Context:
         if rc:
             self._raise(rc, bo.bad_record)
         return bo
+
+    def lanes(self):
+        n = self._lib.bstr_lanes(self._ctx)
+        if n < 0:
+            self._raise(n)
+        return n
+
+    def submit(self, lane, raw, final=True, nbytes=None, offset=0):
+        """Enqueue one batch on `lane` (no wait).  `raw` must stay alive until collect()."""
+        addr, n, keep = self._addr(raw)
+        if nbytes is not None:
+            n = int(nbytes)
+        rc = self._lib.bstr_submit_batch(self._ctx, int(lane), (addr or 0) + int(offset), n, int(bool(final)))
+        if rc:
+            self._raise(rc)
+        return keep
+
+    def collect(self, lane, copy=True):
+        """Wait for the batch on `lane`; returns (output bytes or BatchOut, info)."""
+        bo = BatchOut()
+        rc = self._lib.bstr_collect_batch(self._ctx, int(lane), C.byref(bo))
+        if rc:
+            self._raise(rc, bo.bad_record)
+        info = {"consumed": bo.consumed, "n_records": bo.n_records, "n_selected": bo.n_selected,
+                "out_bytes": bo.out_bytes}
+        if not copy:
+            return bo, info
+        return (C.string_at(bo.out, bo.out_bytes) if bo.out_bytes else b""), info
 
     def match_reads(self, seqs):
         """list of bytes -> uint32 [n, 4] (fstart, rstart, fck, rck); fck = copies << 3 | k."""

@@ -29,7 +29,24 @@ struct DeviceSlot {
     size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres, cap_lb;
 
     int reserve(struct ::bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need);
+    int reserve_generic(struct ::bstr_ctx *ctx, uint64_t nbytes);   // staged-kernel buffers, on demand
     void release();
+};
+
+constexpr int BSTR_LANES_PER_DEVICE = 3;
+
+// One in-flight batch: its own stream, events and buffers on one device.  A batch moves
+// through submit (H2D + kernels + state read-back enqueued) and collect (wait, D2H of the
+// exact output size); lanes of one device overlap each other's copies and kernels.
+struct Lane {
+    DeviceSlot slot;
+    cudaStream_t st;
+    cudaEvent_t ev[8];
+    int dev;                       // CUDA ordinal
+    const uint8_t *raw;            // host input of the batch in flight
+    uint64_t nbytes;
+    int final;
+    bool busy;
 };
 
 }  // namespace bstr
@@ -51,6 +68,9 @@ struct bstr_ctx {
     uint32_t *d_flush; size_t cap_flush;
     std::vector<bstr::DeviceSlot> *bench_slots;   // bstr_bench_resident
     bstr::StreamEngine *engine;    // bstr_run_files (stream_host.cu)
+    bstr::Lane *lanes;             // bstr_submit_batch / bstr_collect_batch, created on first use
+    int n_lanes;
+    void *lock;                    // std::mutex guarding stats and err (worker threads of bstr_run_files)
     bstr_stats stats;
     char err[512];
     bstr_ctx() { memset(this, 0, sizeof(*this)); }
@@ -65,6 +85,10 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
                     cudaEvent_t *ev, bool generic = false);
 int decode_bad(bstr_ctx *ctx, unsigned long long first_bad, int64_t *bad_record);
 void stream_release(bstr_ctx *ctx);
+int lanes_create(bstr_ctx *ctx);
+void lanes_release(bstr_ctx *ctx);
+int lane_submit(bstr_ctx *ctx, Lane &ln, const uint8_t *raw, uint64_t nbytes, int final);
+int lane_collect(bstr_ctx *ctx, Lane &ln, bstr_batch_out *out);
 double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes);
 int pipeline_stage_count(const bstr_ctx *ctx);
 const char *pipeline_stage_name(const bstr_ctx *ctx, int k);

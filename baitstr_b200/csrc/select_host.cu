@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include <vector>
 
 #include "host_common.h"
@@ -20,6 +21,7 @@ namespace bstr {
 
 void set_error(bstr_ctx *ctx, const char *fmt, ...)
 {
+    std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock);
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
@@ -46,26 +48,35 @@ static int grow(bstr_ctx *ctx, void **p, size_t *cap, size_t need, bool pinned_h
 #define GROW(ptr, cap, need, pinned)                                                     \
     do { int rc_ = grow(ctx, (void **)&(ptr), &(cap), (need), (pinned)); if (rc_) return rc_; } while (0)
 
-// size every device buffer for a batch of nbytes raw bytes (worst cases)
+// size the device buffers of the fused path for a batch of nbytes raw bytes (worst cases,
+// see DESIGN.md); the staged generic kernels get theirs in reserve_generic()
 int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
 {
-    const uint64_t max_lines = nbytes + 4;                 // every byte a newline
     const uint64_t max_rec = nbytes / 4 + 2;
-    const uint64_t n_tiles = nbytes / IDX_TILE + 2;
     GROW(d_in_raw, cap_in, nbytes + 2 * IN_SLACK, false);
     d_in = d_in_raw + IN_SLACK;
-    GROW(d_nlpos, cap_nlpos, max_lines * 4, false);
-    GROW(d_tiles, cap_tiles, n_tiles * 4, false);
-    GROW(d_res, cap_res, max_rec * sizeof(ReadResult), false);
-    GROW(d_outlen, cap_outlen, max_rec * 4, false);
-    if (out_need < 2 * nbytes + 4096) out_need = 2 * nbytes + 4096;
+    if (ctx->p.want_results) GROW(d_res, cap_res, max_rec * sizeof(ReadResult), false);
+    if (out_need < nbytes + nbytes / 2 + 4096) out_need = nbytes + nbytes / 2 + 4096;
     GROW(d_out, cap_out, out_need, false);
-    const uint64_t n_tiles_f = nbytes / FW_MINTILE + 2;
+    const uint64_t n_tiles_f = nbytes / (FW_MINTILE < FT_MINTILE ? FW_MINTILE : FT_MINTILE) + 2;
     GROW(d_lb, cap_lb, (2 * n_tiles_f + 2) * 8, false);
     if (!d_state) {
         CUDA_TRY(cudaMalloc((void **)&d_state, sizeof(BatchState) + 64));
         CUDA_TRY(cudaHostAlloc((void **)&h_state, sizeof(BatchState), cudaHostAllocDefault));
     }
+    if (ctx->force_generic) return reserve_generic(ctx, nbytes);
+    return BSTR_OK;
+}
+
+int DeviceSlot::reserve_generic(bstr_ctx *ctx, uint64_t nbytes)
+{
+    const uint64_t max_lines = nbytes + 4;                 // every byte a newline
+    const uint64_t max_rec = nbytes / 4 + 2;
+    const uint64_t n_tiles = nbytes / IDX_TILE + 2;
+    GROW(d_nlpos, cap_nlpos, max_lines * 4, false);
+    GROW(d_tiles, cap_tiles, n_tiles * 4, false);
+    GROW(d_res, cap_res, max_rec * sizeof(ReadResult), false);
+    GROW(d_outlen, cap_outlen, max_rec * 4, false);
     return BSTR_OK;
 }
 
@@ -95,6 +106,7 @@ static int launch_generic(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int fin
                           cudaEvent_t *ev /* 5 events or NULL */)
 {
     const ScanParams prm = scan_params(ctx);
+    { int rc_ = s.reserve_generic(ctx, nbytes); if (rc_) return rc_; }
     const unsigned n_tiles = (unsigned)((nbytes + IDX_TILE - 1) / IDX_TILE);
     unsigned long long *d_total = (unsigned long long *)((uint8_t *)s.d_state + sizeof(BatchState));
     const int rec_blocks = ctx->sm_count * 8;
@@ -286,10 +298,11 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     if (ndev <= 0)
         return fail("bstr_create: no CUDA device available (this library has no CPU fallback)");
     bstr_ctx *ctx = new bstr_ctx();
+    ctx->lock = new std::mutex();
     ctx->p = *p;
     if (ctx->p.kmask == 0) ctx->p.kmask = 0x7C;            // 2..6 (select_STR_reads:134-136)
     ctx->p.kmask &= 0x7C;
-    if (ctx->p.kmask == 0) { delete ctx; return fail("bstr_create: no period in 2..6 selected"); }
+    if (ctx->p.kmask == 0) { delete (std::mutex *)ctx->lock; delete ctx; return fail("bstr_create: no period in 2..6 selected"); }
     if (ctx->p.batch_bytes == 0) ctx->p.batch_bytes = 64ull << 20;
     if (ctx->p.batch_bytes > (2ull << 30)) ctx->p.batch_bytes = 2ull << 30;
     if (ctx->p.n_devices <= 0) {
@@ -298,6 +311,7 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     }
     for (int i = 0; i < ctx->p.n_devices; i++)
         if (ctx->p.devices[i] < 0 || ctx->p.devices[i] >= ndev) {
+            delete (std::mutex *)ctx->lock;
             delete ctx;
             return fail("bstr_create: device ordinal out of range");
         }
@@ -308,6 +322,7 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, ctx->dev);
     if (e != cudaSuccess) {
         if (err && errlen) snprintf(err, errlen, "bstr_create: %s", cudaGetErrorString(e));
+        delete (std::mutex *)ctx->lock;
         delete ctx;
         return nullptr;
     }
@@ -344,11 +359,13 @@ void bstr_destroy(bstr_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->dev);
     stream_release(ctx);
+    lanes_release(ctx);
     ctx->slot.release();
     if (ctx->bench_slots) { for (auto &s : *ctx->bench_slots) s.release(); delete ctx->bench_slots; }
     cudaFree(ctx->d_seqs); cudaFree(ctx->d_off); cudaFree(ctx->d_flush);
     for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete (std::mutex *)ctx->lock;
     delete ctx;
 }
 

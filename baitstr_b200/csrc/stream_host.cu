@@ -1,10 +1,19 @@
 // stream_host.cu -- bstr_run_files: the file loop of the select stage
 // (/root/reference/src/select_STR_reads.pyx:359-370; reader = /root/reference/src/fastq.pyx:48-94).
 //
-// Files are consumed in argv order; ".gz" is decided by the file-name suffix exactly as
-// fastq.pyx:50 does.  The host never parses FASTQ: it moves raw bytes into batches, the
-// device reports how many bytes were whole records, and the unconsumed tail is carried to
-// the front of the next batch.
+// The reference parses a chunk, blocks in pool.map, prints, and only then parses the next
+// chunk (pyx:362-367).  Here three kinds of host threads overlap instead:
+//   reader   (1)        files in argv order, ".gz" by file-name suffix exactly as fastq.pyx:50;
+//                       raw bytes go straight into page-locked batch buffers, cut at a record
+//                       boundary (a whole number of 4-line groups; the host counts '\n', it
+//                       never interprets FASTQ), the partial tail is carried to the next batch
+//   device   (1 / GPU)  bstr lanes: submit (H2D + kernels) up to three batches per GPU, collect
+//                       (D2H of the exact output) the oldest; batches are dealt to whichever
+//                       GPU has a free lane -- reads are independent, there is no collective
+//   writer   (caller)   writes the outputs in batch order to out_fd, "Done processing <path>"
+//                       to err_fd after a file's last batch; the first failing batch in input
+//                       order stops the run (everything before it has been written, as the
+//                       reference prints the chunks before a bad record)
 #include <errno.h>
 #include <fcntl.h>
 #include <stdio.h>
@@ -13,19 +22,30 @@
 #include <unistd.h>
 #include <zlib.h>
 
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <mutex>
+#include <thread>
+#include <vector>
+
 #include "host_common.h"
 
 namespace bstr {
 
-struct StreamEngine {
-    uint8_t *buf;        // pinned staging buffer
+struct PinnedBuf {
+    uint8_t *p;
     size_t cap;
+};
+
+struct StreamEngine {
+    std::vector<PinnedBuf> pool;   // page-locked batch buffers, kept across calls
 };
 
 void stream_release(bstr_ctx *ctx)
 {
     if (!ctx->engine) return;
-    if (ctx->engine->buf) cudaFreeHost(ctx->engine->buf);
+    for (auto &b : ctx->engine->pool) if (b.p) cudaFreeHost(b.p);
     delete ctx->engine;
     ctx->engine = nullptr;
 }
@@ -45,6 +65,9 @@ struct Source {
         } else {
             fd = open(path, O_RDONLY);
             if (fd < 0) return -1;
+#ifdef POSIX_FADV_SEQUENTIAL
+            posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
         }
         return 0;
     }
@@ -82,15 +105,245 @@ static int write_all(int fd, const uint8_t *p, size_t n)
     return 0;
 }
 
-static int ensure_buf(bstr_ctx *ctx, size_t need)
+// number of '\n' in [p, p+n) (auto-vectorised byte compare)
+static uint64_t count_newlines(const uint8_t *p, size_t n)
 {
-    StreamEngine *e = ctx->engine;
-    if (e->cap >= need) return BSTR_OK;
-    uint8_t *nb = nullptr;
-    CUDA_TRY(cudaHostAlloc((void **)&nb, need, cudaHostAllocDefault));
-    if (e->buf) cudaFreeHost(e->buf);
-    e->buf = nb; e->cap = need;
-    return BSTR_OK;
+    uint64_t total = 0;
+    while (n) {
+        const size_t m = n < 4096 ? n : 4096;
+        uint32_t c = 0;
+        for (size_t i = 0; i < m; i++) c += p[i] == '\n';
+        total += c; p += m; n -= m;
+    }
+    return total;
+}
+
+// Largest prefix of buf[0, have) that is a whole number of 4-line groups (0 if none).
+static size_t record_cut(const uint8_t *buf, size_t have)
+{
+    const uint64_t lines = count_newlines(buf, have);
+    uint64_t drop = lines & 3;                 // newlines after the last whole group
+    if (lines < 4) return 0;
+    size_t end = have;
+    // walk back over the partial tail: `drop` newlines, then to just past the previous one
+    const uint8_t *q = (const uint8_t *)memrchr(buf, '\n', end);
+    while (drop--) { end = (size_t)(q - buf); q = (const uint8_t *)memrchr(buf, '\n', end); }
+    return (size_t)(q - buf) + 1;
+}
+
+// One batch travelling reader -> device worker -> writer.
+struct Job {
+    uint64_t seq;
+    int file;
+    PinnedBuf buf;            // input (returned to the pool by the device worker)
+    size_t nbytes;
+    bool final, file_end, reader_error;
+    // filled by the device worker
+    int rc, lane;
+    bstr_batch_out bo;
+    char msg[512];
+};
+
+struct Pipeline {
+    bstr_ctx *ctx;
+    const char *const *paths;
+    int npaths;
+    std::mutex mu;
+    std::condition_variable cv_free, cv_work, cv_done, cv_lane;
+    std::deque<PinnedBuf> free_bufs;
+    size_t bufs_made = 0, bufs_max = 0, buf_cap = 0;
+    std::deque<Job *> work;
+    std::map<uint64_t, Job *> done;
+    std::vector<int> lane_state;          // 0 free, 1 submitted, 2 collected (writer still reads it)
+    bool reader_finished = false, abort = false;
+    uint64_t n_jobs = 0;                  // valid once reader_finished
+};
+
+static PinnedBuf get_buf(Pipeline &P)
+{
+    std::unique_lock<std::mutex> lk(P.mu);
+    for (;;) {
+        if (P.abort) return PinnedBuf{nullptr, 0};
+        if (!P.free_bufs.empty()) { PinnedBuf b = P.free_bufs.front(); P.free_bufs.pop_front(); return b; }
+        if (P.bufs_made < P.bufs_max) {
+            P.bufs_made++;
+            lk.unlock();
+            PinnedBuf b{nullptr, P.buf_cap};
+            if (cudaHostAlloc((void **)&b.p, b.cap, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); b.p = nullptr; b.cap = 0; }
+            return b;
+        }
+        P.cv_free.wait(lk);
+    }
+}
+
+static void put_buf(Pipeline &P, PinnedBuf b)
+{
+    if (!b.p) return;
+    if (b.cap != P.buf_cap) { cudaFreeHost(b.p); return; }      // one-off oversize buffer
+    { std::lock_guard<std::mutex> g(P.mu); P.free_bufs.push_back(b); }
+    P.cv_free.notify_all();
+}
+
+static void emit(Pipeline &P, Job *j)
+{
+    { std::lock_guard<std::mutex> g(P.mu); j->seq = P.n_jobs++; P.work.push_back(j); }
+    P.cv_work.notify_all();
+}
+
+static Job *new_job(int file, PinnedBuf b, size_t nbytes, bool final, bool file_end)
+{
+    Job *j = new Job();
+    memset(j, 0, sizeof(*j));
+    j->file = file; j->buf = b; j->nbytes = nbytes; j->final = final; j->file_end = file_end;
+    j->lane = -1; j->bo.bad_record = -1;
+    return j;
+}
+
+static void reader_fail(Pipeline &P, int file, PinnedBuf b, const char *what, const char *path)
+{
+    Job *j = new_job(file, b, 0, true, true);
+    j->reader_error = true; j->rc = BSTR_ERR_IO;
+    snprintf(j->msg, sizeof(j->msg), "%s %s: %s", what, path, errno ? strerror(errno) : "I/O error");
+    emit(P, j);
+}
+
+static void reader_main(Pipeline *pp)
+{
+    Pipeline &P = *pp;
+    cudaSetDevice(P.ctx->dev);
+    for (int fi = 0; fi < P.npaths; fi++) {
+        Source src;
+        errno = 0;
+        if (src.open_path(P.paths[fi]) != 0) { reader_fail(P, fi, PinnedBuf{nullptr, 0}, "cannot open", P.paths[fi]); break; }
+        PinnedBuf b = get_buf(P);
+        size_t have = 0;
+        bool eof = false, stop = false;
+        while (!stop) {
+            if (!b.p) {                                           // abort, or out of pinned memory
+                bool ab;
+                { std::lock_guard<std::mutex> g(P.mu); ab = P.abort; }
+                if (!ab) { errno = ENOMEM; reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); }
+                stop = true; break;
+            }
+            while (!eof && have < b.cap) {
+                errno = 0;
+                long r = src.read_some(b.p + have, b.cap - have);
+                if (r < 0) { reader_fail(P, fi, b, "read error on", P.paths[fi]); b.p = nullptr; stop = true; break; }
+                if (r == 0) eof = true;
+                have += (size_t)r;
+            }
+            if (stop) break;
+            if (eof) { emit(P, new_job(fi, b, have, true, true)); b.p = nullptr; break; }
+            const size_t cut = record_cut(b.p, have);
+            if (cut == 0) {
+                // not even one whole record in a full buffer: continue in a larger one-off buffer
+                if (b.cap >= (2ull << 30)) {
+                    Job *j = new_job(fi, b, 0, true, true);
+                    j->reader_error = true; j->rc = BSTR_ERR_TOO_LARGE;
+                    snprintf(j->msg, sizeof(j->msg), "%s: record larger than 2 GiB", P.paths[fi]);
+                    emit(P, j); b.p = nullptr; stop = true; break;
+                }
+                PinnedBuf nb{nullptr, b.cap * 2 > (2ull << 30) ? (size_t)(2ull << 30) : b.cap * 2};
+                if (cudaHostAlloc((void **)&nb.p, nb.cap, cudaHostAllocDefault) != cudaSuccess) {
+                    cudaGetLastError(); errno = ENOMEM;
+                    reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); b.p = nullptr; stop = true; break;
+                }
+                memcpy(nb.p, b.p, have);
+                put_buf(P, b);
+                b = nb;
+                continue;
+            }
+            PinnedBuf nb = get_buf(P);
+            if (!nb.p) {
+                bool ab;
+                { std::lock_guard<std::mutex> g(P.mu); ab = P.abort; }
+                if (!ab) { errno = ENOMEM; reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); }
+                else put_buf(P, b);
+                b.p = nullptr; stop = true; break;
+            }
+            memcpy(nb.p, b.p + cut, have - cut);
+            emit(P, new_job(fi, b, cut, false, false));
+            b = nb; have -= cut;
+        }
+        src.close_all();
+        if (b.p) put_buf(P, b);
+        bool ab;
+        { std::lock_guard<std::mutex> g(P.mu); ab = P.abort; }
+        if (stop || ab) break;
+    }
+    { std::lock_guard<std::mutex> g(P.mu); P.reader_finished = true; }
+    P.cv_work.notify_all(); P.cv_done.notify_all();
+}
+
+static void publish(Pipeline &P, Job *j)
+{
+    { std::lock_guard<std::mutex> g(P.mu); P.done[j->seq] = j; }
+    P.cv_done.notify_all();
+}
+
+// One thread per GPU: keeps up to BSTR_LANES_PER_DEVICE batches in flight on its device.
+static void device_main(Pipeline *pp, int d)
+{
+    Pipeline &P = *pp;
+    bstr_ctx *ctx = P.ctx;
+    const int ndev = ctx->p.n_devices;
+    std::deque<std::pair<int, Job *>> inflight;
+    for (;;) {
+        Job *job = nullptr;
+        int lane = -1;
+        bool quit = false, aborting = false;
+        {
+            std::unique_lock<std::mutex> lk(P.mu);
+            for (;;) {
+                if (P.abort) { aborting = true; break; }
+                lane = -1;
+                for (int l = d; l < ctx->n_lanes; l += ndev) if (P.lane_state[l] == 0) { lane = l; break; }
+                if (lane >= 0 && !P.work.empty()) { job = P.work.front(); P.work.pop_front(); P.lane_state[lane] = 1; break; }
+                if (!inflight.empty()) break;                       // nothing to submit: collect the oldest
+                if (P.reader_finished && P.work.empty()) { quit = true; break; }
+                P.cv_work.wait(lk);
+            }
+        }
+        if (aborting) {
+            for (auto &it : inflight) {                             // leave the device idle
+                bstr_batch_out bo;
+                lane_collect(ctx, ctx->lanes[it.first], &bo);
+                put_buf(P, it.second->buf);
+                delete it.second;
+            }
+            return;
+        }
+        if (quit) return;
+        if (job) {
+            if (job->reader_error || job->nbytes == 0) {            // nothing for the GPU
+                put_buf(P, job->buf); job->buf.p = nullptr;
+                { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = 0; }
+                publish(P, job);
+                continue;
+            }
+            const int rc = lane_submit(ctx, ctx->lanes[lane], job->buf.p, job->nbytes, job->final ? 1 : 0);
+            if (rc) {
+                job->rc = rc;
+                { std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock); snprintf(job->msg, sizeof(job->msg), "%s", ctx->err); }
+                put_buf(P, job->buf); job->buf.p = nullptr;
+                { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = 0; }
+                publish(P, job);
+                continue;
+            }
+            inflight.push_back(std::make_pair(lane, job));
+            continue;
+        }
+        const int cl = inflight.front().first;
+        Job *j = inflight.front().second;
+        inflight.pop_front();
+        j->rc = lane_collect(ctx, ctx->lanes[cl], &j->bo);
+        if (j->rc) { std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock); snprintf(j->msg, sizeof(j->msg), "%s", ctx->err); }
+        put_buf(P, j->buf); j->buf.p = nullptr;                     // the H2D copy is complete
+        const bool hold = j->rc == BSTR_OK && j->bo.out_bytes;      // the writer reads the lane's pinned output
+        j->lane = hold ? cl : -1;
+        { std::lock_guard<std::mutex> g(P.mu); P.lane_state[cl] = hold ? 2 : 0; }
+        publish(P, j);
+    }
 }
 
 }  // namespace bstr
@@ -102,65 +355,78 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
 {
     if (!ctx || (!paths && npaths)) return BSTR_ERR_PARAM;
     CUDA_TRY(cudaSetDevice(ctx->dev));
-    if (!ctx->engine) { ctx->engine = new StreamEngine(); ctx->engine->buf = nullptr; ctx->engine->cap = 0; }
-    int rc = ensure_buf(ctx, ctx->p.batch_bytes);
+    int rc = lanes_create(ctx);
     if (rc) return rc;
-    for (int fi = 0; fi < npaths; fi++) {
-        Source src;
-        if (src.open_path(paths[fi]) != 0) {
-            set_error(ctx, "cannot open %s: %s", paths[fi], strerror(errno));
-            return BSTR_ERR_IO;
-        }
-        size_t have = 0;
-        uint64_t rec_base = 0;
-        bool eof = false;
-        while (!eof || have) {
-            StreamEngine *e = ctx->engine;
-            while (!eof && have < e->cap) {
-                long r = src.read_some(e->buf + have, e->cap - have);
-                if (r < 0) { src.close_all(); set_error(ctx, "read error on %s", paths[fi]); return BSTR_ERR_IO; }
-                if (r == 0) eof = true;
-                have += (size_t)r;
-            }
-            if (have == 0) break;
-            bstr_batch_out bo;
-            rc = bstr_scan_batch(ctx, e->buf, have, eof ? 1 : 0, &bo);
-            if (rc) {
-                if (bo.bad_record >= 0) {
-                    char tmp[400];
-                    snprintf(tmp, sizeof(tmp), "%s", ctx->err);
-                    set_error(ctx, "%s: record %llu: %s", paths[fi],
-                              (unsigned long long)(rec_base + (uint64_t)bo.bad_record), tmp);
-                }
-                src.close_all();
-                return rc;
-            }
-            if (bo.out_bytes && write_all(out_fd, bo.out, bo.out_bytes) != 0) {
-                src.close_all(); set_error(ctx, "write error: %s", strerror(errno)); return BSTR_ERR_IO;
-            }
-            rec_base += bo.n_records;
-            if (eof) { have = 0; break; }
-            if (bo.consumed == 0) {
-                // one record larger than the whole batch buffer: enlarge and retry
-                if (e->cap >= (2ull << 30)) { src.close_all(); set_error(ctx, "%s: record larger than 2 GiB", paths[fi]); return BSTR_ERR_TOO_LARGE; }
-                size_t ncap = e->cap * 2;
-                if (ncap > (2ull << 30)) ncap = 2ull << 30;
-                uint8_t *nb = nullptr;
-                CUDA_TRY(cudaHostAlloc((void **)&nb, ncap, cudaHostAllocDefault));
-                memcpy(nb, e->buf, have);
-                cudaFreeHost(e->buf);
-                e->buf = nb; e->cap = ncap;
-                continue;
-            }
-            memmove(e->buf, e->buf + bo.consumed, have - bo.consumed);
-            have -= bo.consumed;
-        }
-        src.close_all();
-        if (err_fd >= 0) {
-            char line[4200];
-            int n = snprintf(line, sizeof(line), "Done processing %s\n", paths[fi]);   // pyx:370
-            if (n > 0) write_all(err_fd, (const uint8_t *)line, (size_t)n);
-        }
+    if (!ctx->engine) ctx->engine = new StreamEngine();
+    Pipeline P;
+    P.ctx = ctx; P.paths = paths; P.npaths = npaths;
+    P.buf_cap = ctx->p.batch_bytes;
+    P.bufs_max = (size_t)ctx->n_lanes + 2;
+    P.lane_state.assign((size_t)ctx->n_lanes, 0);
+    for (auto &b : ctx->engine->pool) {
+        if (b.cap == P.buf_cap && P.bufs_made < P.bufs_max) { P.free_bufs.push_back(b); P.bufs_made++; }
+        else cudaFreeHost(b.p);
     }
-    return BSTR_OK;
+    ctx->engine->pool.clear();
+
+    std::thread reader(reader_main, &P);
+    std::vector<std::thread> workers;
+    for (int d = 0; d < ctx->p.n_devices; d++) workers.emplace_back(device_main, &P, d);
+
+    // writer: batch order == input order (select_STR_reads.pyx:363-367)
+    uint64_t next = 0, rec_base = 0;
+    int result = BSTR_OK;
+    char errmsg[sizeof(ctx->err)] = "";
+    for (;;) {
+        Job *j = nullptr;
+        {
+            std::unique_lock<std::mutex> lk(P.mu);
+            for (;;) {
+                auto it = P.done.find(next);
+                if (it != P.done.end()) { j = it->second; P.done.erase(it); break; }
+                if (P.reader_finished && next == P.n_jobs) break;
+                P.cv_done.wait(lk);
+            }
+        }
+        if (!j) break;
+        if (j->rc) {
+            result = j->rc;
+            if (j->bo.bad_record >= 0)
+                snprintf(errmsg, sizeof(errmsg), "%.200s: record %llu: %.250s", paths[j->file],
+                         (unsigned long long)(rec_base + (uint64_t)j->bo.bad_record), j->msg);
+            else snprintf(errmsg, sizeof(errmsg), "%.500s", j->msg);
+        } else if (j->bo.out_bytes && write_all(out_fd, j->bo.out, j->bo.out_bytes) != 0) {
+            result = BSTR_ERR_IO;
+            snprintf(errmsg, sizeof(errmsg), "write error: %s", strerror(errno));
+        }
+        if (j->lane >= 0) {
+            { std::lock_guard<std::mutex> g(P.mu); P.lane_state[j->lane] = 0; }
+            P.cv_work.notify_all();
+        }
+        if (result) { delete j; break; }
+        rec_base += j->bo.n_records;
+        if (j->file_end) {
+            rec_base = 0;
+            if (err_fd >= 0) {
+                char line[4200];
+                int n = snprintf(line, sizeof(line), "Done processing %s\n", paths[j->file]);   // pyx:370
+                if (n > 0) write_all(err_fd, (const uint8_t *)line, (size_t)n);
+            }
+        }
+        delete j;
+        next++;
+    }
+    if (result) {
+        { std::lock_guard<std::mutex> g(P.mu); P.abort = true; }
+        P.cv_work.notify_all(); P.cv_free.notify_all();
+    }
+    reader.join();
+    for (auto &w : workers) w.join();
+    for (Job *j : P.work) { if (j->buf.p) put_buf(P, j->buf); delete j; }
+    for (auto &kv : P.done) { if (kv.second->buf.p) put_buf(P, kv.second->buf); delete kv.second; }
+    for (auto &b : P.free_bufs) ctx->engine->pool.push_back(b);
+    for (int l = 0; l < ctx->n_lanes; l++) ctx->lanes[l].busy = false;
+    CUDA_TRY(cudaSetDevice(ctx->dev));
+    if (result) set_error(ctx, "%s", errmsg);
+    return result;
 }

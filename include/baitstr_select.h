@@ -117,6 +117,18 @@ int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npaths, int out_
 int bstr_scan_batch(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int final,
                     bstr_batch_out *out);
 
+/* The same work as bstr_scan_batch, split in two so that several batches are in flight:
+ * "pinned double-buffered H2D/D2H batches on CUDA streams".  A context has bstr_lanes()
+ * lanes (3 per device; lane l runs on device l % n_devices).  bstr_submit_batch enqueues the
+ * H2D copy, the kernels and the state read-back on the lane's stream and returns at once;
+ * bstr_collect_batch waits for that batch and copies back exactly the bytes produced.  `raw`
+ * must stay valid (and should be page-locked, bstr_host_alloc) until the collect; the output
+ * stays valid until the next submit on the same lane.  Replaces the blocking
+ * pool.map(func, chunk) of select_STR_reads.pyx:363; the caller keeps batch order. */
+int bstr_lanes(bstr_ctx *ctx);
+int bstr_submit_batch(bstr_ctx *ctx, int lane, const uint8_t *raw, uint64_t nbytes, int final);
+int bstr_collect_batch(bstr_ctx *ctx, int lane, bstr_batch_out *out);
+
 /* Per-read matcher hook (the GPU counterpart of ProcessSequence / MatchPatternsAndReportBest,
  * select_STR_reads.pyx:106,294): nreads sequences concatenated in `seqs`, read i occupying
  * [offsets[i], offsets[i+1]).  Bases may be lower case; they are not validated here. */

@@ -330,3 +330,81 @@ def test_fused_tile_geometry_and_fallback(capi):
                 assert ei.value.code == ERRMAP[oe.code] and ei.value.bad_record == oe.record
             else:
                 assert ctx.scan_batch(raw)[0] == want
+
+
+def test_async_lanes_keep_order_and_reuse(capi):
+    """bstr_submit_batch / bstr_collect_batch: several batches in flight, any lane, outputs
+    identical to the blocking call; lanes are reusable and refuse a double submit."""
+    chunks = [util.synth_fastq(3000 + 500 * i, 100 + 10 * i, seed=40 + i, p_str=0.5) for i in range(7)]
+    want = [oracle.select_buffer(c) for c in chunks]
+    with capi.Context() as ctx:
+        nl = ctx.lanes()
+        assert nl >= 3
+        keep, got, inflight = {}, [None] * len(chunks), []
+        for i, c in enumerate(chunks):
+            lane = i % nl
+            if len(inflight) == nl:
+                j, l = inflight.pop(0)
+                got[j] = ctx.collect(l)[0]
+            keep[lane] = ctx.submit(lane, c)
+            inflight.append((i, lane))
+        with pytest.raises(capi.BstrError):
+            ctx.submit(inflight[0][1], chunks[0])            # lane still busy
+        for j, l in inflight:
+            got[j] = ctx.collect(l)[0]
+        assert got == want
+        with pytest.raises(capi.BstrError):
+            ctx.collect(0)                                   # nothing in flight
+        assert ctx.scan_batch(chunks[0])[0] == want[0]        # blocking call still fine
+
+
+def test_run_files_edge_files_and_errors(capi, tmp_path):
+    """Empty file, file without trailing newline, a bad record deep in the second file: the
+    batches before the failing one are written (as the reference prints earlier chunks),
+    the error names file and record, later files are not touched."""
+    a = util.synth_fastq(2500, 100, seed=21, tag="a")
+    b = util.synth_fastq(2500, 100, seed=22, tag="b")
+    pa, pe, pb, pc = (str(tmp_path / n) for n in ("a.fq", "empty.fq", "b.fq", "c.fq"))
+    open(pa, "wb").write(a[:-1])                              # last newline missing
+    open(pe, "wb").write(b"")
+    open(pb, "wb").write(b)
+    open(pc, "wb").write(a)
+    want = oracle.select_buffer(a[:-1]) + oracle.select_buffer(b)
+    outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+    with capi.Context(batch_bytes=96 << 10) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+        ctx.run_files([pa, pe, pb], out_fd=fo.fileno(), err_fd=fe.fileno())
+    assert open(outp, "rb").read() == want
+    assert open(errp).read() == "".join("Done processing %s\n" % p for p in (pa, pe, pb))
+    # bad separator in record 1777 of b
+    lines = b.split(b"\n")
+    assert lines[4 * 1777 + 2] == b"+"
+    lines[4 * 1777 + 2] = b"-"
+    open(pb, "wb").write(b"\n".join(lines))
+    with capi.Context(batch_bytes=96 << 10) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files([pa, pb, pc], out_fd=fo.fileno(), err_fd=fe.fileno())
+        assert ei.value.code == -12 and "b.fq" in str(ei.value) and "record 1777" in str(ei.value)
+        # the context survives and can run again
+        with open(outp + "2", "wb") as fo2:
+            ctx.run_files([pa], out_fd=fo2.fileno(), err_fd=-1)
+        assert open(outp + "2", "rb").read() == oracle.select_buffer(a[:-1])
+    got = open(outp, "rb").read()
+    full = oracle.select_buffer(a[:-1]) + oracle.select_buffer(b"\n".join(lines[:4 * 1777]) + b"\n")
+    assert full.startswith(got) and got.startswith(oracle.select_buffer(a[:-1]))
+    assert open(errp).read() == "Done processing %s\n" % pa
+    # missing file
+    with capi.Context() as ctx, open(outp, "wb") as fo:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files([pa, str(tmp_path / "nope.fq")], out_fd=fo.fileno(), err_fd=-1)
+        assert ei.value.code == -4
+    assert open(outp, "rb").read() == oracle.select_buffer(a[:-1])
+
+
+def test_warp_kernel_variant(capi, monkeypatch):
+    """k_fused_warp (BSTR_KERNEL=warp), the warp-autonomous variant kept for tuning, stays exact."""
+    monkeypatch.setenv("BSTR_KERNEL", "warp")
+    for L, vary in ((100, False), (250, False), (180, True)):
+        raw = util.synth_fastq(20000, L, seed=300 + L, p_str=0.5, p_n=0.05, vary_len=vary)
+        for kw in (dict(), dict(n=3, rmhm=True)):
+            with capi.Context(**kw) as ctx:
+                assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, **kw)
