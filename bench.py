@@ -110,31 +110,23 @@ def barrier(dist):
 
 
 def max_over_ranks(dist, x):
-    if dist is None:
-        return x
-    import torch
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    from baitstr_b200 import shard
+    return shard.reduce_scalar(dist, x, "max")
 
 
 def sum_over_ranks(dist, x):
-    if dist is None:
-        return x
-    import torch
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    return float(t.item())
+    from baitstr_b200 import shard
+    return shard.reduce_scalar(dist, x, "sum")
 
 
 def make_batches(rank, reads_per_gpu, batch_reads):
     """This rank's share of the workload as pinned raw-FASTQ batches (mate 1 then mate 2)."""
-    from baitstr_b200 import capi, synth
+    from baitstr_b200 import capi, shard, synth
     rb = synth.record_bytes(CFG, READ_LEN)
-    half = reads_per_gpu // 2
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     batches = []
     for mate in (1, 2):
-        first, left = rank * half, half
+        first, left = shard.read_range(world * (reads_per_gpu // 2), rank, world)
         while left > 0:
             cnt = min(batch_reads, left)
             buf = capi.PinnedBuffer(rb * cnt)
