@@ -24,6 +24,7 @@ constexpr int FT_MAXCPT = 16;                  // 16-byte chunks per thread in t
 constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
 constexpr int FT_MAXREGION = 65504;            // line positions are 16-bit
 constexpr int FT_MINTILE = 8192;
+constexpr int FT_MLP = 8;                      // 16-byte loads in flight per thread while staging
 constexpr int FT_DEFTILE = 40960;
 constexpr int FT_MAXSMEM = 200 * 1024;         // opt-in dynamic shared memory limit of the kernel
 
@@ -257,6 +258,7 @@ __device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileG
     return cnt;
 }
 
+template <int WMAX>
 __global__ void __launch_bounds__(FT_MAXTHREADS, 2)
 k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
              BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
@@ -285,17 +287,17 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     const bool last = tile == ntiles - 1;
 
     // ---- A: stage the tile (+ look-ahead) in shared memory, 16-byte coalesced loads -------
-    for (uint32_t cb = 0; cb < g.chunks; cb += 4 * nthr) {
-        uint4 v[4];
+    for (uint32_t cb = 0; cb < g.chunks; cb += FT_MLP * nthr) {
+        uint4 v[FT_MLP];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < FT_MLP; u++) {
             const uint32_t c = cb + u * nthr + tid;
             const uint64_t off = ts + 16ull * c;
             v[u] = make_uint4(0, 0, 0, 0);
             if (c < g.chunks && off < n) v[u] = __ldg(reinterpret_cast<const uint4 *>(in + off));
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < FT_MLP; u++) {
             const uint32_t c = cb + u * nthr + tid;
             if (c < g.chunks) *reinterpret_cast<uint4 *>(sin + 16 * c) = v[u];
         }
@@ -401,7 +403,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
             else if (!(exp_mask & 2) && bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
             else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
             if (bad) atomicMin(&st->first_bad, (r << 8) | (unsigned)bad);
-            else if (!(exp_mask & 1)) match_read(sin + ln.s1, L, prm, wmax, f, rc);
+            else if (!(exp_mask & 1)) match_read<WMAX>(sin + ln.s1, L, prm, wmax, f, rc);
             sel = f.k && rc.k;
             ReadResult o;
             o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : 0;

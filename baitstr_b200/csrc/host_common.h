@@ -25,7 +25,7 @@ struct DeviceSlot {
     BatchState *d_state, *h_state;
     uint8_t *h_out;                // pinned
     ReadResult *h_res;             // pinned
-    double rec_bytes;              // average record size of the batch in d_in (tile geometry)
+    double rec_bytes, hdr_bytes;   // average record size / first header length of the batch in d_in (tile geometry)
     size_t cap_in, cap_nlpos, cap_tiles, cap_res, cap_outlen, cap_out, cap_hout, cap_hres, cap_lb;
 
     int reserve(struct ::bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need);
@@ -57,9 +57,7 @@ struct bstr_ctx {
     int sm_count;
     int exp_mask;                  // BSTR_EXP: phase-skipping bits for profiling experiments
     uint32_t geom_tile, geom_threads, geom_stage;   // BSTR_GEOM overrides (0 = automatic)
-    uint32_t wgeom_tile, wgeom_ovl, wgeom_stage;    // BSTR_WGEOM overrides (0 = automatic)
-    double wgeom_recs;             // records per warp tile
-    bool use_cta_kernel;           // default; BSTR_KERNEL=warp selects k_fused_warp
+    int force_wmax;                // BSTR_WMAX: 2, 4 or 8 (0 = from the record size)
     bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
     cudaStream_t stream;
     cudaEvent_t ev[8];
@@ -89,7 +87,7 @@ int lanes_create(bstr_ctx *ctx);
 void lanes_release(bstr_ctx *ctx);
 int lane_submit(bstr_ctx *ctx, Lane &ln, const uint8_t *raw, uint64_t nbytes, int final);
 int lane_collect(bstr_ctx *ctx, Lane &ln, bstr_batch_out *out);
-double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes);
+double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes, double *hdr_bytes);
 int pipeline_stage_count(const bstr_ctx *ctx);
 const char *pipeline_stage_name(const bstr_ctx *ctx, int k);
 int pipeline_launches_per_batch(const bstr_ctx *ctx);

@@ -208,10 +208,9 @@ __global__ void k_finish_index(uint32_t *nlpos, const unsigned long long *n_newl
 }
 
 __device__ __forceinline__ int dec_digits(uint32_t v)
-{
-    int d = 1;
-    while (v >= 10) { v /= 10; d++; }
-    return d;
+{   // branch-free: every lane of a warp runs the same nine compares
+    return 1 + (v >= 10u) + (v >= 100u) + (v >= 1000u) + (v >= 10000u) + (v >= 100000u) +
+           (v >= 1000000u) + (v >= 10000000u) + (v >= 100000000u) + (v >= 1000000000u);
 }
 
 // bytes PrintSequence emits for one selected record
@@ -287,6 +286,13 @@ k_scan_records(const uint8_t *in, const uint32_t *nlpos, BatchState *st, ScanPar
 
 __device__ __forceinline__ uint8_t *put_dec(uint8_t *p, uint32_t v)
 {
+    if (v < 1000u) {                           // copies, starts and ends of short reads: no loop
+        const uint32_t h = v / 100u, r = v - 100u * h, t = r / 10u, u = r - 10u * t;
+        if (v >= 100u) *p++ = (uint8_t)('0' + h);
+        if (v >= 10u) *p++ = (uint8_t)('0' + t);
+        *p++ = (uint8_t)('0' + u);
+        return p;
+    }
     const int d = dec_digits(v);
     for (int i = d - 1; i >= 0; i--) { p[i] = (uint8_t)('0' + v % 10); v /= 10; }
     return p + d;

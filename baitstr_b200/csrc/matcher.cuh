@@ -579,13 +579,16 @@ __device__ __forceinline__ int window_words(int L, const ScanParams &prm)
 }
 
 // Dispatch on the window width.  `wmax` is warp-uniform (max over the warp's reads) so the
-// branch does not diverge.
+// branch does not diverge.  WMAX (2, 4 or 8) is the widest bit-parallel window compiled into
+// the calling kernel: a kernel built for short reads carries neither the code nor the
+// registers of the wide windows; reads that need more words take the exact byte path.
+template <int WMAX = 8>
 __device__ __forceinline__ void match_read(const uint8_t *seq, int L, const ScanParams &prm,
                                            int wmax, Hit &fwd, Hit &rc)
 {
     if (wmax <= 2) match_read_bits<2>(seq, L, prm, fwd, rc);
-    else if (wmax <= 4) match_read_bits<4>(seq, L, prm, fwd, rc);
-    else if (wmax <= 8) match_read_bits<8>(seq, L, prm, fwd, rc);
+    else if (WMAX >= 4 && wmax <= 4) match_read_bits<(WMAX >= 4 ? 4 : 2)>(seq, L, prm, fwd, rc);
+    else if (WMAX >= 8 && wmax <= 8) match_read_bits<(WMAX >= 8 ? 8 : 2)>(seq, L, prm, fwd, rc);
     else match_read_bytes(seq, L, prm, fwd, rc);
 }
 

@@ -15,7 +15,6 @@
 #include "host_common.h"
 #include "kernels_v1.cuh"
 #include "fused.cuh"
-#include "fused_warp.cuh"
 
 namespace bstr {
 
@@ -58,7 +57,7 @@ int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
     if (ctx->p.want_results) GROW(d_res, cap_res, max_rec * sizeof(ReadResult), false);
     if (out_need < nbytes + nbytes / 2 + 4096) out_need = nbytes + nbytes / 2 + 4096;
     GROW(d_out, cap_out, out_need, false);
-    const uint64_t n_tiles_f = nbytes / (FW_MINTILE < FT_MINTILE ? FW_MINTILE : FT_MINTILE) + 2;
+    const uint64_t n_tiles_f = nbytes / FT_MINTILE + 2;
     GROW(d_lb, cap_lb, (2 * n_tiles_f + 2) * 8, false);
     if (!d_state) {
         CUDA_TRY(cudaMalloc((void **)&d_state, sizeof(BatchState) + 64));
@@ -127,10 +126,18 @@ static int launch_generic(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int fin
     return BSTR_OK;
 }
 
+cudaError_t set_tile_attrs()
+{
+    cudaError_t e = cudaFuncSetAttribute(k_fused_tile<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_tile<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_tile<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
+    return e;
+}
+
 // Tile geometry for a batch whose records average `rec_bytes` bytes (fused.cuh: TileGeom).
 // The tile is sized so that it owns about as many records as the CTA has threads; the
 // CTA size follows from the tile size.  BSTR_GEOM=tile,threads[,stage] overrides (sweeps).
-TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes)
+TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threads)
 {
     if (rec_bytes < 16) rec_bytes = 16;
     uint32_t tile = ctx->geom_tile ? ctx->geom_tile : FT_DEFTILE;
@@ -146,7 +153,7 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes)
     const uint32_t min_thr = ((chunks + FT_MAXCPT - 1) / FT_MAXCPT + 31) & ~31u;
     if (threads < min_thr) threads = min_thr;
     if (threads < 64) threads = 64;
-    if (threads > FT_MAXTHREADS) threads = FT_MAXTHREADS;
+    if (threads > max_threads) threads = max_threads & ~31u;
     uint32_t stage = ctx->geom_stage;
     if (!stage) stage = (uint32_t)(tile * (1.0 + 48.0 / rec_bytes) + rec_bytes) + 2048;
     stage = (stage + 15) & ~15u;
@@ -156,12 +163,18 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes)
     return g;
 }
 
-// first bytes of a host batch -> average record size (4 lines per record)
-double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes)
+// first bytes of a host batch -> average record size (4 lines per record); *hdr_bytes gets
+// the length of the first line (header), which separates read length from record size
+double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes, double *hdr_bytes)
 {
     const uint64_t span = nbytes < (128u << 10) ? nbytes : (128u << 10);
     uint64_t lines = 0;
-    for (const uint8_t *p = raw, *e = raw + span; p < e && (p = (const uint8_t *)memchr(p, '\n', (size_t)(e - p))); p++) lines++;
+    const uint8_t *first = nullptr;
+    for (const uint8_t *p = raw, *e = raw + span; p < e && (p = (const uint8_t *)memchr(p, '\n', (size_t)(e - p))); p++) {
+        if (!first) first = p;
+        lines++;
+    }
+    if (hdr_bytes) *hdr_bytes = first ? (double)(first - raw) : 0.0;
     return lines >= 8 ? 4.0 * (double)span / (double)lines : 256.0;
 }
 
@@ -171,7 +184,14 @@ static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final
                         cudaEvent_t *ev)
 {
     const ScanParams prm = scan_params(ctx);
-    const TileGeom g = pick_geometry(ctx, s.rec_bytes);
+    // widest bit-parallel window the batch is expected to need (longer reads stay exact through
+    // the byte path): L = (record - header - 6) / 2, window = L - 2 (f - 6) for the default
+    // algorithm; 10 % margin for reads longer than the average
+    const int fe = prm.altalgo && prm.f > 6 ? prm.f - 6 : 0;
+    const double win = (s.rec_bytes - s.hdr_bytes - 6.0) * 0.5 * 1.10 - 2.0 * fe;
+    const int wmax = ctx->force_wmax ? ctx->force_wmax : (win <= 64 ? 2 : (win <= 128 ? 4 : 8));
+    const uint32_t max_threads = FT_MAXTHREADS;
+    const TileGeom g = pick_geometry(ctx, s.rec_bytes, max_threads);
     const uint32_t n_tiles = (uint32_t)((nbytes + g.tile - 1) / g.tile);
     unsigned long long *lb_lines = s.d_lb, *lb_out = s.d_lb + n_tiles, *ticket = s.d_lb + 2 * (size_t)n_tiles;
     const uint32_t lb_words = 2 * n_tiles + 1;
@@ -179,58 +199,16 @@ static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final
     if (ev) cudaEventRecord(ev[0], st);
     k_fused_init<<<init_blocks, 256, 0, st>>>(s.d_state, s.d_lb, lb_words);
     if (ev) cudaEventRecord(ev[1], st);
-    if (n_tiles)
-        k_fused_tile<<<n_tiles, g.threads, g.smem_bytes, st>>>(
-            s.d_in, nbytes, final, prm, ctx->p.illumina_quals, s.d_state, lb_lines, lb_out, ticket,
-            n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out, ctx->exp_mask, g);
-    if (ev) { cudaEventRecord(ev[2], st); cudaEventRecord(ev[4], st); }
-    CUDA_TRY(cudaGetLastError());
-    return BSTR_OK;
-}
-
-// Geometry of the warp-autonomous kernel (fused_warp.cuh): a warp tile holds ~30 records so
-// that a 32-lane round of the per-record phases is full but rarely needs a second round; the
-// look-ahead covers a record that starts on the tile's last byte.
-// BSTR_WGEOM=tile,lookahead,stage overrides (sweeps).
-WarpGeom pick_warp_geometry(const bstr_ctx *ctx, double rec_bytes)
-{
-    if (rec_bytes < 16) rec_bytes = 16;
-    uint32_t ovl = ctx->wgeom_ovl ? ctx->wgeom_ovl : (uint32_t)(3.0 * rec_bytes);
-    ovl = (ovl + 15) & ~15u;
-    if (ovl < 1024) ovl = 1024;
-    if (ovl > 8192) ovl = 8192;
-    uint32_t tile = ctx->wgeom_tile ? ctx->wgeom_tile : (uint32_t)(ctx->wgeom_recs * rec_bytes);
-    tile &= ~15u;
-    if (tile + ovl > (uint32_t)FW_MAXREGION) tile = FW_MAXREGION - ovl;
-    if (tile < (uint32_t)FW_MINTILE) tile = FW_MINTILE;
-    uint32_t stage = ctx->wgeom_stage ? ctx->wgeom_stage
-                                      : (uint32_t)(tile * (1.0 + 48.0 / rec_bytes) + rec_bytes) + 256;
-    stage = (stage + 15) & ~15u;
-    return make_warp_geometry(tile, ovl, stage);
-}
-
-static int launch_fused_warp(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cudaStream_t st,
-                             cudaEvent_t *ev)
-{
-    const ScanParams prm = scan_params(ctx);
-    const WarpGeom g = pick_warp_geometry(ctx, s.rec_bytes);
-    const uint32_t n_tiles = (uint32_t)((nbytes + g.tile - 1) / g.tile);
-    unsigned long long *lb_lines = s.d_lb, *lb_out = s.d_lb + n_tiles, *ticket = s.d_lb + 2 * (size_t)n_tiles;
-    const uint32_t lb_words = 2 * n_tiles + 1;
-    const uint32_t init_blocks = (lb_words + 255) / 256 < 64 ? (lb_words + 255) / 256 : 64;
-    const uint32_t smem = FW_WARPS * g.warp_bytes;
-    uint32_t per_sm = (uint32_t)(FW_MAXSMEM / (smem + 1024));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm > 16) per_sm = 16;
-    uint32_t grid = (uint32_t)ctx->sm_count * per_sm;             // persistent warps
-    if (grid > (n_tiles + FW_WARPS - 1) / FW_WARPS) grid = (n_tiles + FW_WARPS - 1) / FW_WARPS;
-    if (ev) cudaEventRecord(ev[0], st);
-    k_fused_init<<<init_blocks, 256, 0, st>>>(s.d_state, s.d_lb, lb_words);
-    if (ev) cudaEventRecord(ev[1], st);
-    if (n_tiles)
-        k_fused_warp<<<grid, FW_THREADS, smem, st>>>(
-            s.d_in, nbytes, final, prm, ctx->p.illumina_quals, s.d_state, lb_lines, lb_out, ticket,
-            n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out, ctx->exp_mask, g);
+#define BSTR_LAUNCH_TILE(W)                                                                          \
+    k_fused_tile<W><<<n_tiles, g.threads, g.smem_bytes, st>>>(                                       \
+        s.d_in, nbytes, final, prm, ctx->p.illumina_quals, s.d_state, lb_lines, lb_out, ticket,      \
+        n_tiles, ctx->p.want_results ? s.d_res : nullptr, s.d_out, s.cap_out, ctx->exp_mask, g)
+    if (n_tiles) {
+        if (wmax <= 2) BSTR_LAUNCH_TILE(2);
+        else if (wmax <= 4) BSTR_LAUNCH_TILE(4);
+        else BSTR_LAUNCH_TILE(8);
+    }
+#undef BSTR_LAUNCH_TILE
     if (ev) { cudaEventRecord(ev[2], st); cudaEventRecord(ev[4], st); }
     CUDA_TRY(cudaGetLastError());
     return BSTR_OK;
@@ -241,8 +219,7 @@ int launch_pipeline(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final, cu
                     cudaEvent_t *ev, bool generic)
 {
     if (generic || ctx->force_generic) return launch_generic(ctx, s, nbytes, final, st, ev);
-    return ctx->use_cta_kernel ? launch_fused(ctx, s, nbytes, final, st, ev)
-                               : launch_fused_warp(ctx, s, nbytes, final, st, ev);
+    return launch_fused(ctx, s, nbytes, final, st, ev);
 }
 
 int pipeline_stage_count(const bstr_ctx *ctx) { return ctx->force_generic ? 4 : 2; }
@@ -250,8 +227,7 @@ const char *pipeline_stage_name(const bstr_ctx *ctx, int k)
 {
     static const char *gen[4] = {"index(newlines)", "k_scan_records", "k_scan_outlen", "k_format_records"};
     static const char *fus[2] = {"k_fused_init", "k_fused_tile"};
-    static const char *fw[2] = {"k_fused_init", "k_fused_warp"};
-    return ctx->force_generic ? gen[k] : (ctx->use_cta_kernel ? fus[k] : fw[k]);
+    return ctx->force_generic ? gen[k] : fus[k];
 }
 int pipeline_launches_per_batch(const bstr_ctx *ctx) { return ctx->force_generic ? 7 : 2; }
 
@@ -335,16 +311,8 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
         ctx->exp_mask = ex ? atoi(ex) : 0;
         const char *ge = getenv("BSTR_GEOM");          // tile,threads[,stage] (0 = automatic)
         if (ge) sscanf(ge, "%u,%u,%u", &ctx->geom_tile, &ctx->geom_threads, &ctx->geom_stage);
-        const char *wg = getenv("BSTR_WGEOM");         // tile,lookahead,stage (0 = automatic)
-        if (wg) sscanf(wg, "%u,%u,%u", &ctx->wgeom_tile, &ctx->wgeom_ovl, &ctx->wgeom_stage);
-        const char *wr = getenv("BSTR_WRECS");         // records per warp tile (default 30.5)
-        ctx->wgeom_recs = wr ? atof(wr) : 30.5;
-        const char *kk = getenv("BSTR_KERNEL");        // "warp": the warp-autonomous variant (fused_warp.cuh)
-        ctx->use_cta_kernel = !(kk && strcmp(kk, "warp") == 0);
     }
-    e = cudaFuncSetAttribute(k_fused_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_fused_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, FW_MAXSMEM);
+    e = set_tile_attrs();
     if (e != cudaSuccess) {
         if (err && errlen) snprintf(err, errlen, "bstr_create: %s", cudaGetErrorString(e));
         bstr_destroy(ctx);

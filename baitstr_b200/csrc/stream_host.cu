@@ -29,9 +29,16 @@
 #include <thread>
 #include <vector>
 
+#include <chrono>
+
 #include "host_common.h"
 
 namespace bstr {
+
+static inline double now_ms()
+{
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 struct PinnedBuf {
     uint8_t *p;
@@ -157,6 +164,7 @@ struct Pipeline {
     std::vector<int> lane_state;          // 0 free, 1 submitted, 2 collected (writer still reads it)
     bool reader_finished = false, abort = false;
     uint64_t n_jobs = 0;                  // valid once reader_finished
+    double t_read = 0, t_cut = 0, t_alloc = 0, t_bufwait = 0;   // reader thread, ms (BSTR_TRACE)
 };
 
 static PinnedBuf get_buf(Pipeline &P)
@@ -169,10 +177,14 @@ static PinnedBuf get_buf(Pipeline &P)
             P.bufs_made++;
             lk.unlock();
             PinnedBuf b{nullptr, P.buf_cap};
+            const double t0 = now_ms();
             if (cudaHostAlloc((void **)&b.p, b.cap, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); b.p = nullptr; b.cap = 0; }
+            P.t_alloc += now_ms() - t0;
             return b;
         }
+        const double t0 = now_ms();
         P.cv_free.wait(lk);
+        P.t_bufwait += now_ms() - t0;
     }
 }
 
@@ -225,6 +237,7 @@ static void reader_main(Pipeline *pp)
                 if (!ab) { errno = ENOMEM; reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); }
                 stop = true; break;
             }
+            const double tr0 = now_ms();
             while (!eof && have < b.cap) {
                 errno = 0;
                 long r = src.read_some(b.p + have, b.cap - have);
@@ -232,9 +245,12 @@ static void reader_main(Pipeline *pp)
                 if (r == 0) eof = true;
                 have += (size_t)r;
             }
+            P.t_read += now_ms() - tr0;
             if (stop) break;
             if (eof) { emit(P, new_job(fi, b, have, true, true)); b.p = nullptr; break; }
+            const double tc0 = now_ms();
             const size_t cut = record_cut(b.p, have);
+            P.t_cut += now_ms() - tc0;
             if (cut == 0) {
                 // not even one whole record in a full buffer: continue in a larger one-off buffer
                 if (b.cap >= (2ull << 30)) {
@@ -354,9 +370,12 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
                               int err_fd)
 {
     if (!ctx || (!paths && npaths)) return BSTR_ERR_PARAM;
+    const double t_begin = now_ms();
     CUDA_TRY(cudaSetDevice(ctx->dev));
     int rc = lanes_create(ctx);
     if (rc) return rc;
+    const double t_lanes = now_ms();
+    double t_wait = 0, t_write = 0;
     if (!ctx->engine) ctx->engine = new StreamEngine();
     Pipeline P;
     P.ctx = ctx; P.paths = paths; P.npaths = npaths;
@@ -381,14 +400,17 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
         Job *j = nullptr;
         {
             std::unique_lock<std::mutex> lk(P.mu);
+            const double tw0 = now_ms();
             for (;;) {
                 auto it = P.done.find(next);
                 if (it != P.done.end()) { j = it->second; P.done.erase(it); break; }
                 if (P.reader_finished && next == P.n_jobs) break;
                 P.cv_done.wait(lk);
             }
+            t_wait += now_ms() - tw0;
         }
         if (!j) break;
+        const double tx0 = now_ms();
         if (j->rc) {
             result = j->rc;
             if (j->bo.bad_record >= 0)
@@ -403,6 +425,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
             { std::lock_guard<std::mutex> g(P.mu); P.lane_state[j->lane] = 0; }
             P.cv_work.notify_all();
         }
+        t_write += now_ms() - tx0;
         if (result) { delete j; break; }
         rec_base += j->bo.n_records;
         if (j->file_end) {
@@ -427,6 +450,12 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     for (auto &b : P.free_bufs) ctx->engine->pool.push_back(b);
     for (int l = 0; l < ctx->n_lanes; l++) ctx->lanes[l].busy = false;
     CUDA_TRY(cudaSetDevice(ctx->dev));
+    ctx->stats.wall_ms += now_ms() - t_begin;
+    if (getenv("BSTR_TRACE"))
+        fprintf(stderr, "[bstr] run_files %.1f ms: lanes %.1f | reader: read %.1f cut %.1f pinned-alloc %.1f buffer-wait %.1f | "
+                "writer: wait %.1f write %.1f | device: h2d %.1f kernels %.1f d2h %.1f (summed over %llu batches)\n",
+                now_ms() - t_begin, t_lanes - t_begin, P.t_read, P.t_cut, P.t_alloc, P.t_bufwait, t_wait, t_write,
+                ctx->stats.h2d_ms, ctx->stats.kernel_ms, ctx->stats.d2h_ms, (unsigned long long)ctx->stats.batches);
     if (result) set_error(ctx, "%s", errmsg);
     return result;
 }

@@ -398,13 +398,3 @@ def test_run_files_edge_files_and_errors(capi, tmp_path):
             ctx.run_files([pa, str(tmp_path / "nope.fq")], out_fd=fo.fileno(), err_fd=-1)
         assert ei.value.code == -4
     assert open(outp, "rb").read() == oracle.select_buffer(a[:-1])
-
-
-def test_warp_kernel_variant(capi, monkeypatch):
-    """k_fused_warp (BSTR_KERNEL=warp), the warp-autonomous variant kept for tuning, stays exact."""
-    monkeypatch.setenv("BSTR_KERNEL", "warp")
-    for L, vary in ((100, False), (250, False), (180, True)):
-        raw = util.synth_fastq(20000, L, seed=300 + L, p_str=0.5, p_n=0.05, vary_len=vary)
-        for kw in (dict(), dict(n=3, rmhm=True)):
-            with capi.Context(**kw) as ctx:
-                assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, **kw)

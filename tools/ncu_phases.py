@@ -9,9 +9,9 @@ RANGES = {
  'matcher.cuh': [(44,131,'match: bit helpers'),(143,243,'match: encode planes'),(260,357,'match: scan_period'),
                  (359,413,'match: pick winner'),(415,486,'match: match_read_bits'),(488,590,'match: long/dispatch'),(592,640,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
- 'fused.cuh': [(52,80,'lookback'),(83,90,'index: nl_mask'),(93,114,'block scan'),(126,133,'record lines'),(138,196,'format: copy'),
-               (198,229,'A stage'),(230,271,'B index fill'),(272,320,'C lookback1+bookkeeping'),(321,358,'D per-record glue'),
-               (359,379,'E offsets+lookback2'),(380,388,'F format glue'),(389,401,'G flush')],
+ 'fused.cuh': [(77,106,'lookback'),(108,116,'index: nl_mask'),(118,140,'block scan'),(151,160,'record lines'),(163,225,'format: copy'),
+               (227,260,'B index chunks'),(262,306,'A stage'),(307,333,'B index fill'),(334,381,'C lookback1+bookkeeping'),(382,420,'D per-record glue'),
+               (421,440,'E offsets+lookback2'),(441,450,'F format glue'),(451,470,'G flush')],
 }
 PRIO = ['matcher.cuh', 'kernels_v1.cuh', 'fused.cuh']
 fname = cols = cur = None; seen = []; stack = defaultdict(dict); inst = {}; samp = {}; thr = {}; stalls = defaultdict(lambda: defaultdict(float))
