@@ -64,7 +64,7 @@ inline TileGeom make_geometry(uint32_t tile, uint32_t threads, uint32_t stage)
     g.recmax = 2 * threads; g.nlmax = 5 * g.recmax + 64; g.stage = stage;
     uint32_t o = (sizeof(FusedVars) + 15) & ~15u;
     g.off_in = o;       o += 16 + g.region + 32;
-    g.off_stage = o;    o += g.stage + 32;
+    g.off_stage = o;    o += g.stage + 48;
     g.off_rec = o;      o += g.recmax * 16;
     g.off_outoff = o;   o += g.recmax * 4;
     g.off_nl = o;       o += (g.nlmax + 8) * 2;
@@ -72,17 +72,21 @@ inline TileGeom make_geometry(uint32_t tile, uint32_t threads, uint32_t stage)
     return g;
 }
 
-// Decoupled look-back, run by one full warp.  st[] was zeroed before the launch.  Returns
-// the exclusive prefix of `agg` over the tiles before `tile`.
-__device__ __forceinline__ unsigned long long warp_lookback(unsigned long long *st, int tile,
-                                                            unsigned long long agg)
+// Decoupled look-back in two steps so that work can be placed between them.
+// lookback_publish (one thread): make this tile's aggregate visible at once -- successors then
+// only wait for tiles whose aggregate is not known yet.  st[] was zeroed before the launch.
+__device__ __forceinline__ void lookback_publish(unsigned long long *st, int tile, unsigned long long agg)
+{
+    atomicExch(&st[tile], (tile == 0 ? LB_INC : LB_AGG) | agg);
+}
+
+// lookback_resolve (one full warp, after lookback_publish of the same tile): returns the
+// exclusive prefix of `agg` over the tiles before `tile` and publishes the inclusive prefix.
+__device__ __forceinline__ unsigned long long lookback_resolve(unsigned long long *st, int tile,
+                                                               unsigned long long agg)
 {
     const int lane = threadIdx.x & 31;
-    if (tile == 0) {
-        if (lane == 0) atomicExch(&st[0], LB_INC | agg);
-        return 0;
-    }
-    if (lane == 0) atomicExch(&st[tile], LB_AGG | agg);
+    if (tile == 0) return 0;
     unsigned long long excl = 0;
     int hi = tile - 1;
     for (;;) {
@@ -102,6 +106,14 @@ __device__ __forceinline__ unsigned long long warp_lookback(unsigned long long *
     }
     if (lane == 0) atomicExch(&st[tile], LB_INC | (excl + agg));
     return excl;
+}
+
+__device__ __forceinline__ unsigned long long warp_lookback(unsigned long long *st, int tile,
+                                                            unsigned long long agg)
+{
+    if ((threadIdx.x & 31) == 0) lookback_publish(st, tile, agg);
+    __syncwarp();
+    return lookback_resolve(st, tile, agg);
 }
 
 // 16-bit mask of the '\n' bytes of one 16-byte chunk
@@ -418,47 +430,68 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     }
     __syncthreads();
 
-    // ---- E: output offsets: records inside the tile, then the tile (look-back #2) ---------
+    // ---- E: output offsets of the records inside the tile; the tile's byte count is published
+    //         at once, the look-back over the earlier tiles is resolved AFTER formatting: a tile
+    //         needs the totals of every tile before it, i.e. it waits for the slowest matcher
+    //         among several hundred tiles in flight (11 % of the kernel when waited for here)
     const uint32_t o0 = s_outoff[2 * tid], o1 = s_outoff[2 * tid + 1];
     uint32_t total;
     const uint32_t oex = block_excl_scan(o0 + o1, S.warp_tmp, &total);
     s_outoff[2 * tid] = oex;
     s_outoff[2 * tid + 1] = oex + o0;
-    if (total > g.stage - 16) { bail = true; total = 0; nproc = 0; }
-    if (bail && tid == 0) atomicExch(&st->fallback, 1ull);
+    if (total > g.stage - 32 && !(exp_mask & 16)) { bail = true; total = 0; nproc = 0; }   // bit 16: occupancy experiments with a dummy stage (needs bits 4|8)
+    if (tid == 0) {
+        if (bail) atomicExch(&st->fallback, 1ull);
+        lookback_publish(lb_out, (int)tile, total);
+    }
+    if (lane == 0 && nsel && !bail) atomicAdd(&st->n_selected, (unsigned long long)nsel);
+    __syncthreads();
+
+    // ---- F: PrintSequence into the staging buffer (dense, from offset 0) ---------------------
+    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += nthr) {
+        const ReadResult rr = s_rec[j];
+        if (rr.fck == 0) continue;
+        const RecordLines ln = tile_record_lines(s_nl, (int)(i0 + 4 * j));
+        format_record_words(sin, ln, rr, illumina, stage + s_outoff[j]);
+    }
     if (wid == 0) {
-        const unsigned long long ob = warp_lookback(lb_out, (int)tile, total);
+        // exp bit 32 (timing experiments only): no look-back wait, tiles write at disjoint fake offsets
+        const unsigned long long ob = (exp_mask & 32) ? (unsigned long long)tile * g.stage
+                                                      : lookback_resolve(lb_out, (int)tile, total);
         if (lane == 0) {
             S.out_base = ob;
             if (last) st->out_bytes = ob + total;
         }
     }
-    if (lane == 0 && nsel && !bail) atomicAdd(&st->n_selected, (unsigned long long)nsel);
     __syncthreads();
     const unsigned long long out_base = S.out_base;
     if (total == 0 || out_base + total > outcap) return;     // host grows the buffer and re-runs
 
-    // ---- F: PrintSequence into the staging buffer (same 16-byte phase as the destination) --
-    const uint32_t a0 = (uint32_t)(out_base & 15);
-    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += nthr) {
-        const ReadResult rr = s_rec[j];
-        if (rr.fck == 0) continue;
-        const RecordLines ln = tile_record_lines(s_nl, (int)(i0 + 4 * j));
-        format_record_words(sin, ln, rr, illumina, stage + a0 + s_outoff[j]);
-    }
-    __syncthreads();
-
-    // ---- G: flush the staging buffer with aligned 16-byte stores ----------------------------
+    // ---- G: flush the staging buffer: aligned 16-byte stores; the source is shifted by the
+    //         destination's phase (uniform over the CTA, so the word select does not diverge) ----
     if (exp_mask & 8) return;
     uint8_t *dst = out + out_base;
-    const uint32_t head = min(total, (16u - a0) & 15u);
-    if (tid < head) dst[tid] = stage[a0 + tid];
+    const uint32_t head = min(total, (16u - (uint32_t)(out_base & 15)) & 15u);
+    if (tid < head) dst[tid] = stage[tid];
     const uint32_t nchunk = (total - head) >> 4;
-    const uint8_t *sb = stage + a0 + head;
-    for (uint32_t c = tid; c < nchunk; c += nthr)
-        *reinterpret_cast<uint4 *>(dst + head + 16 * c) = *reinterpret_cast<const uint4 *>(sb + 16 * c);
+    const uint32_t q = head >> 2, r8 = 8 * (head & 3);
+#define BSTR_FLUSH(Q0, W0, W1, W2, W3, W4)                                                          \
+    if (q == Q0)                                                                                    \
+        for (uint32_t c = tid; c < nchunk; c += nthr) {                                             \
+            const uint4 A = *reinterpret_cast<const uint4 *>(stage + 16 * c);                       \
+            const uint4 B = *reinterpret_cast<const uint4 *>(stage + 16 * c + 16);                  \
+            uint4 o;                                                                                \
+            o.x = __funnelshift_r(W0, W1, r8); o.y = __funnelshift_r(W1, W2, r8);                   \
+            o.z = __funnelshift_r(W2, W3, r8); o.w = __funnelshift_r(W3, W4, r8);                   \
+            *reinterpret_cast<uint4 *>(dst + head + 16 * c) = o;                                    \
+        }
+    BSTR_FLUSH(0, A.x, A.y, A.z, A.w, B.x)
+    BSTR_FLUSH(1, A.y, A.z, A.w, B.x, B.y)
+    BSTR_FLUSH(2, A.z, A.w, B.x, B.y, B.z)
+    BSTR_FLUSH(3, A.w, B.x, B.y, B.z, B.w)
+#undef BSTR_FLUSH
     const uint32_t done = head + (nchunk << 4);
-    if (tid < total - done) dst[done + tid] = stage[a0 + done + tid];
+    if (tid < total - done) dst[done + tid] = stage[done + tid];
 }
 
 }  // namespace bstr
