@@ -24,7 +24,6 @@ constexpr int FT_MAXCPT = 16;                  // 16-byte chunks per thread in t
 constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
 constexpr int FT_MAXREGION = 65504;            // line positions are 16-bit
 constexpr int FT_MINTILE = 8192;
-constexpr int FT_MLP = 8;                      // 16-byte loads in flight per thread while staging
 constexpr int FT_DEFTILE = 40960;
 constexpr int FT_MAXSMEM = 200 * 1024;         // opt-in dynamic shared memory limit of the kernel
 
@@ -50,6 +49,7 @@ struct TileGeom {
 };
 
 struct FusedVars {                                      // at offset 0 of the dynamic smem
+    unsigned long long mbar;                            // mbarrier of the tile's bulk copy
     long long gbase;                                    // global index of local line 0
     unsigned long long out_base;
     uint32_t tile, pad0;
@@ -70,6 +70,28 @@ inline TileGeom make_geometry(uint32_t tile, uint32_t threads, uint32_t stage)
     g.off_nl = o;       o += (g.nlmax + 8) * 2;
     g.smem_bytes = (o + 15) & ~15u;
     return g;
+}
+
+// ---- TMA bulk copy global -> shared (cp.async.bulk, SASS UBLKCP) with an mbarrier ----------
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t arrivals)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gsrc, uint32_t bytes, unsigned long long *bar)
+{   // one thread: arm the barrier with the byte count, then one copy instruction for the whole tile
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
+{
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    } while (!done);
 }
 
 // Decoupled look-back in two steps so that work can be placed between them.
@@ -286,7 +308,10 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     uint32_t *const s_outoff = reinterpret_cast<uint32_t *>(fused_smem + g.off_outoff);
     uint16_t *const s_nl = reinterpret_cast<uint16_t *>(fused_smem + g.off_nl);   // newline position + 1
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nthr = blockDim.x;
-    if (tid == 0) S.tile = (uint32_t)atomicAdd(ticket, 1ull);
+    if (tid == 0) {
+        S.tile = (uint32_t)atomicAdd(ticket, 1ull);
+        mbar_init(&S.mbar, 1);
+    }
     if (tid < 4) {
         reinterpret_cast<uint32_t *>(in_raw)[tid] = 0u;
         reinterpret_cast<uint32_t *>(sin + g.region)[tid] = 0u;
@@ -298,22 +323,15 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     const bool reach = ts + g.region >= n;           // the staged window covers the batch end
     const bool last = tile == ntiles - 1;
 
-    // ---- A: stage the tile (+ look-ahead) in shared memory, 16-byte coalesced loads -------
-    for (uint32_t cb = 0; cb < g.chunks; cb += FT_MLP * nthr) {
-        uint4 v[FT_MLP];
-#pragma unroll
-        for (int u = 0; u < FT_MLP; u++) {
-            const uint32_t c = cb + u * nthr + tid;
-            const uint64_t off = ts + 16ull * c;
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (c < g.chunks && off < n) v[u] = __ldg(reinterpret_cast<const uint4 *>(in + off));
-        }
-#pragma unroll
-        for (int u = 0; u < FT_MLP; u++) {
-            const uint32_t c = cb + u * nthr + tid;
-            if (c < g.chunks) *reinterpret_cast<uint4 *>(sin + 16 * c) = v[u];
-        }
-    }
+    // ---- A: stage the tile (+ look-ahead) in shared memory: ONE bulk copy (TMA, cp.async.bulk)
+    //         issued by one thread, completion on an mbarrier; every input byte is read from HBM
+    //         once.  Past the batch end the device buffer holds >= 16 zero bytes (IN_SLACK), the
+    //         rest of the window is zero-filled here.
+    const uint32_t nb = reach ? (uint32_t)((n - ts + 15) & ~15ull) : g.region;   // bytes to fetch
+    if (tid == 0) bulk_load(sin, in + ts, nb, &S.mbar);
+    for (uint32_t c = nb / 16 + tid; c < g.chunks; c += nthr)
+        *reinterpret_cast<uint4 *>(sin + 16 * c) = make_uint4(0, 0, 0, 0);
+    mbar_wait(&S.mbar, 0);
     __syncthreads();
 
     // ---- B: line index of the window -----------------------------------------------------
