@@ -215,7 +215,7 @@ __device__ __forceinline__ uint8_t *copy_xform(uint8_t *d, const uint8_t *s, int
     while (n > 0 && ((uintptr_t)d & 3)) { *d++ = xform_byte<MODE>(*s++); n--; }
     const int nw = n >> 2;
     if (nw > 0) {
-        const uint32_t *sp = (const uint32_t *)((uintptr_t)s & ~(uintptr_t)3);
+        const uint32_t *sp = (const uint32_t *)(s - ((uintptr_t)s & 3));   // keeps s's address space (LDS, not LD)
         const int sh = (int)((uintptr_t)s & 3) * 8;
         uint32_t *dp = (uint32_t *)d;
         uint32_t lo = sp[0];

@@ -158,8 +158,10 @@ template <int W>
 __device__ __forceinline__ void encode_window(const uint8_t *src, int Gn, Planes<W> &P,
                                               Bits<W> &dotless_n /* N positions */)
 {
+    // aligned base by pointer arithmetic (not an integer round trip), so that the compiler keeps
+    // the address space of `src` and emits LDS for shared-memory callers instead of generic LD
     const uintptr_t addr = (uintptr_t)src;
-    const uint32_t *wp = (const uint32_t *)(addr & ~(uintptr_t)3);
+    const uint32_t *wp = (const uint32_t *)(src - (addr & 3));
     const int mis8 = (int)(addr & 3) * 8;
 #pragma unroll
     for (int i = 0; i < W; i++) {
@@ -612,7 +614,7 @@ __device__ __forceinline__ uint32_t swar_invalid(uint32_t w)
 __device__ __forceinline__ bool bases_invalid(const uint8_t *p, int L)
 {
     const uintptr_t a = (uintptr_t)p;
-    const uint32_t *wp = (const uint32_t *)(a & ~(uintptr_t)3);
+    const uint32_t *wp = (const uint32_t *)(p - (a & 3));          // keeps p's address space (LDS, not LD)
     if (L <= 0) return false;
     const int head = (int)(a & 3), total = head + L, nw = (total + 3) >> 2;
     // bytes outside the range are replaced by 'A'; only the first and last word need it

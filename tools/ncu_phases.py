@@ -9,9 +9,9 @@ RANGES = {
  'matcher.cuh': [(44,131,'match: bit helpers'),(143,243,'match: encode planes'),(260,357,'match: scan_period'),
                  (359,413,'match: pick winner'),(415,486,'match: match_read_bits'),(488,590,'match: long/dispatch'),(592,640,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
- 'fused.cuh': [(77,106,'lookback'),(108,116,'index: nl_mask'),(118,140,'block scan'),(151,160,'record lines'),(163,225,'format: copy'),
-               (227,260,'B index chunks'),(262,306,'A stage'),(307,333,'B index fill'),(334,381,'C lookback1+bookkeeping'),(382,420,'D per-record glue'),
-               (421,440,'E offsets+lookback2'),(441,450,'F format glue'),(451,470,'G flush')],
+ 'fused.cuh': [(76,98,'tma/mbarrier'),(100,140,'lookback'),(142,150,'index: nl_mask'),(152,174,'block scan'),(185,195,'record lines'),(197,259,'format: copy'),
+               (261,294,'B index chunks'),(296,336,'A stage'),(337,363,'B index fill'),(364,411,'C lookback1+bookkeeping'),(412,450,'D per-record glue'),
+               (451,467,'E offsets'),(468,487,'F format glue + lookback2'),(488,520,'G flush')],
 }
 PRIO = ['matcher.cuh', 'kernels_v1.cuh', 'fused.cuh']
 fname = cols = cur = None; seen = []; stack = defaultdict(dict); inst = {}; samp = {}; thr = {}; stalls = defaultdict(lambda: defaultdict(float))
@@ -26,7 +26,7 @@ for row in csv.reader(open(sys.argv[1])):
         sc = [(i, c) for i, c in enumerate(cols) if c.startswith("stall_") and "Not Issued" not in c]; continue
     if cols is None or row[0] == "Function Name": continue
     if row[0].strip().isdigit(): cur = int(row[0])
-    if row[2].strip():
+    if len(row) > 2 and row[2].strip().startswith('0x'):
         a = row[2].strip(); stack[a].setdefault(fname, cur)
         try:
             inst[a] = float(row[ci] or 0); samp[a] = float(row[cs] or 0); thr[a] = float(row[ct] or 0)
