@@ -219,7 +219,16 @@ __device__ __forceinline__ uint8_t *copy_xform(uint8_t *d, const uint8_t *s, int
         const int sh = (int)((uintptr_t)s & 3) * 8;
         uint32_t *dp = (uint32_t *)d;
         uint32_t lo = sp[0];
-        for (int i = 0; i < nw; i++) {
+        int i = 0;
+        for (; i + 4 <= nw; i += 4) {                       // 16 bytes per trip: 4 LDS, 4 SHF, 4 STS
+            const uint32_t w1 = sp[i + 1], w2 = sp[i + 2], w3 = sp[i + 3], w4 = sp[i + 4];
+            dp[i] = xform_word<MODE>(__funnelshift_r(lo, w1, sh));
+            dp[i + 1] = xform_word<MODE>(__funnelshift_r(w1, w2, sh));
+            dp[i + 2] = xform_word<MODE>(__funnelshift_r(w2, w3, sh));
+            dp[i + 3] = xform_word<MODE>(__funnelshift_r(w3, w4, sh));
+            lo = w4;
+        }
+        for (; i < nw; i++) {
             const uint32_t hi = sp[i + 1];
             dp[i] = xform_word<MODE>(__funnelshift_r(lo, hi, sh));
             lo = hi;
