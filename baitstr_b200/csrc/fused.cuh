@@ -370,14 +370,36 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
         if (tid == 0 && shift) s_nl[0] = 0;
     }
 
-    // ---- C: global line number of the tile's first line (look-back #1) ---------------------
-    if (wid == 0) {
-        const unsigned long long base = warp_lookback(lb_lines, (int)tile, real_own);
-        if (lane == 0) S.gbase = tile == 0 ? -1ll : (long long)base;
+    // ---- C: which local lines start records?  That needs the global line number of the tile's
+    //         first line (look-back #1) only modulo 4, and a valid FASTQ tile gives the phase
+    //         away: a header line starts with '@' and the line two below with '+', while a
+    //         non-empty sequence line can start with neither.  If exactly one phase fits the
+    //         first two records of the window, the records are processed with it at once and
+    //         warp 0 -- the scan warp, it owns no records -- resolves the look-back meanwhile;
+    //         the guess is verified afterwards (mismatch: the batch goes to the generic
+    //         kernels).  Tiles that touch the batch end, and tile 0, take no guess.
+    if (tid == 0) lookback_publish(lb_lines, (int)tile, real_own);
+    __syncthreads();                                  // s_nl complete
+    uint32_t phi = 0, nfit = 0;
+    if (!reach && tile != 0 && !bail && !(exp_mask & 64)) {
+#pragma unroll
+        for (uint32_t p = 0; p < 4; p++) {
+            bool fit = p + 7 < cnt_all;               // two whole records visible
+            if (fit)
+                fit = sin[s_nl[p]] == '@' && sin[s_nl[p + 2]] == '+' && sin[s_nl[p + 4]] == '@' && sin[s_nl[p + 6]] == '+';
+            if (fit) { phi = p; nfit++; }
+        }
     }
-    __syncthreads();
-    const long long gbase = S.gbase;
-    const long long G = gbase + (long long)cnt_all;  // lines of the whole batch, if `reach`
+    const bool spec = nfit == 1;                      // CTA-uniform: every thread reads the same bytes
+    if (!spec) {
+        if (wid == 0) {
+            const unsigned long long base = lookback_resolve(lb_lines, (int)tile, real_own);
+            if (lane == 0) S.gbase = tile == 0 ? -1ll : (long long)base;
+        }
+        __syncthreads();
+    }
+    long long gbase = spec ? 0ll : S.gbase;           // spec: known after phase D
+    const long long G = gbase + (long long)cnt_all;   // lines of the whole batch, if `reach` (never with spec)
     if (final && reach && (G & 3) == 3 && !bail) {
         // EOF after the separator line: accepted with an empty quality string
         // (readline() returns '' at fastq.pyx:89)
@@ -394,16 +416,12 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
             atomicMax(&st->consumed, (unsigned long long)n);
         }
     }
-    const uint32_t i0 = (uint32_t)((3 - gbase) & 3);
+    const uint32_t i0 = spec ? phi : (uint32_t)((3 - gbase) & 3);
     const uint32_t nrec_own = cnt_own > i0 ? (cnt_own - i0 + 3) / 4 : 0u;
     uint32_t nproc = cnt_all >= i0 + 5 ? (cnt_all - 1 - i0) / 4 : 0u;
     if (nproc > nrec_own) nproc = nrec_own;
     if (nproc < nrec_own && !reach) bail = true;      // a record runs past the look-ahead
     if (nproc > g.recmax) bail = true;
-    if (!bail && nrec_own && tid == 0) {
-        const uint32_t iL = i0 + 4 * (nrec_own - 1);
-        if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + s_nl[iL]);
-    }
     if (!bail && final && reach && nproc < nrec_own && tid == 0) {
         // a record cut short by EOF: the reference still tests its header (fastq.pyx:77) and a
         // complete second line (fastq.pyx:81) before the missing line raises (fastq.pyx:86)
@@ -418,44 +436,54 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     if (bail) nproc = 0;
     __syncthreads();                                  // s_nl complete (virtual entry included)
 
-    // ---- D: per record: fastq.next() checks + both-strand match (thread per record) --------
+    // ---- D: per record: fastq.next() checks + both-strand match (thread per record; warp 0
+    //         resolves look-back #1 instead).  A failed check is kept in the record's slot
+    //         (fck = 0, rstart = code) and reported in phase F, when the record index is known.
+    const uint32_t rthr = nthr - 32, rtid = tid - 32;
     uint32_t nsel = 0;
-    for (uint32_t jb = 0; jb < g.recmax; jb += nthr) {
-        const uint32_t j = jb + tid;
-        const bool live = j < nproc;
-        if (jb >= nproc) {                            // CTA-uniform: nothing left in this round
-            s_outoff[j] = 0;
-            continue;
+    if (wid == 0) {
+        if (spec) {
+            const unsigned long long base = lookback_resolve(lb_lines, (int)tile, real_own);
+            if (lane == 0) S.gbase = (long long)base;
         }
-        RecordLines ln = {};
-        int L = 0;
-        if (live) { ln = tile_record_lines(s_nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
-        const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
-        Hit f, rc;
-        f.k = rc.k = 0; f.copies = rc.copies = f.start = rc.start = 0;
-        bool sel = false;
-        uint32_t olen = 0;
-        if (live) {
-            const unsigned long long r = (unsigned long long)((gbase + (long long)(i0 + 4 * j) + 1) >> 2);
-            int bad = 0;
-            if (sin[ln.s0] != '@') bad = BAD_HEADER;                       // fastq.pyx:77
-            else if (!(exp_mask & 2) && bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
-            else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
-            if (bad) atomicMin(&st->first_bad, (r << 8) | (unsigned)bad);
-            else if (!(exp_mask & 1)) match_read<WMAX>(sin + ln.s1, L, prm, wmax, f, rc);
-            sel = f.k && rc.k;
-            ReadResult o;
-            o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : 0;
-            o.fck = sel ? ((uint32_t)f.copies << 3 | f.k) : 0;
-            o.rck = sel ? ((uint32_t)rc.copies << 3 | rc.k) : 0;
-            s_rec[j] = o;
-            if (res) res[r] = o;
-            if (sel) olen = record_out_len(ln.e0 - ln.s0 - 1, L, ln.e3 - ln.s3, f, rc);
+        for (uint32_t j = nproc + lane; j < g.recmax; j += 32) s_outoff[j] = 0;
+    } else {
+        for (uint32_t jb = 0; jb < nproc; jb += rthr) {
+            const uint32_t j = jb + rtid;
+            const bool live = j < nproc;
+            RecordLines ln = {};
+            int L = 0;
+            if (live) { ln = tile_record_lines(s_nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
+            const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
+            Hit f, rc;
+            f.k = rc.k = 0; f.copies = rc.copies = f.start = rc.start = 0;
+            bool sel = false;
+            if (live) {
+                int bad = 0;
+                if (sin[ln.s0] != '@') bad = BAD_HEADER;                       // fastq.pyx:77
+                else if (!(exp_mask & 2) && bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
+                else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
+                if (!bad && !(exp_mask & 1)) match_read<WMAX>(sin + ln.s1, L, prm, wmax, f, rc);
+                sel = f.k && rc.k;
+                ReadResult o;
+                o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : (uint32_t)bad;
+                o.fck = sel ? ((uint32_t)f.copies << 3 | f.k) : 0;
+                o.rck = sel ? ((uint32_t)rc.copies << 3 | rc.k) : 0;
+                s_rec[j] = o;
+                s_outoff[j] = sel ? record_out_len(ln.e0 - ln.s0 - 1, L, ln.e3 - ln.s3, f, rc) : 0u;
+            }
+            nsel += __popc(__ballot_sync(0xFFFFFFFFu, sel));
         }
-        s_outoff[j] = olen;
-        nsel += __popc(__ballot_sync(0xFFFFFFFFu, sel));
     }
     __syncthreads();
+    if (spec) {
+        gbase = S.gbase;
+        if ((uint32_t)((3 - gbase) & 3) != i0) bail = true;     // wrong guess: generic kernels redo the batch
+    }
+    if (!bail && nrec_own && tid == 0) {
+        const uint32_t iL = i0 + 4 * (nrec_own - 1);
+        if (!(shift && iL == 0)) atomicMax(&st->consumed, ts + s_nl[iL]);
+    }
 
     // ---- E: output offsets of the records inside the tile; the tile's byte count is published
     //         at once, the look-back over the earlier tiles is resolved AFTER formatting: a tile
@@ -466,21 +494,33 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     const uint32_t oex = block_excl_scan(o0 + o1, S.warp_tmp, &total);
     s_outoff[2 * tid] = oex;
     s_outoff[2 * tid + 1] = oex + o0;
+    if (bail) { total = 0; nproc = 0; }
     if (total > g.stage - 32 && !(exp_mask & 16)) { bail = true; total = 0; nproc = 0; }   // bit 16: occupancy experiments with a dummy stage (needs bits 4|8)
     if (tid == 0) {
         if (bail) atomicExch(&st->fallback, 1ull);
         lookback_publish(lb_out, (int)tile, total);
     }
-    if (lane == 0 && nsel && !bail) atomicAdd(&st->n_selected, (unsigned long long)nsel);
+    if (lane == 0 && nsel && !bail && wid != 0) atomicAdd(&st->n_selected, (unsigned long long)nsel);
     __syncthreads();
 
     // ---- F: PrintSequence into the staging buffer (dense, from offset 0) ---------------------
-    for (uint32_t j = tid; j < nproc && !(exp_mask & 4); j += nthr) {
-        const ReadResult rr = s_rec[j];
-        if (rr.fck == 0) continue;
-        const RecordLines ln = tile_record_lines(s_nl, (int)(i0 + 4 * j));
-        format_record_words(sin, ln, rr, illumina, stage + s_outoff[j]);
-    }
+    if (wid != 0)
+        for (uint32_t j = rtid; j < nproc; j += rthr) {
+            const ReadResult rr = s_rec[j];
+            const unsigned long long r = (unsigned long long)((gbase + (long long)(i0 + 4 * j) + 1) >> 2);
+            if (res) {
+                ReadResult o = rr;
+                if (o.fck == 0) o.rstart = 0;
+                res[r] = o;
+            }
+            if (rr.fck == 0) {
+                if (rr.rstart) atomicMin(&st->first_bad, (r << 8) | rr.rstart);
+                continue;
+            }
+            if (exp_mask & 4) continue;
+            const RecordLines ln = tile_record_lines(s_nl, (int)(i0 + 4 * j));
+            format_record_words(sin, ln, rr, illumina, stage + s_outoff[j]);
+        }
     if (wid == 0) {
         // exp bit 32 (timing experiments only): no look-back wait, tiles write at disjoint fake offsets
         const unsigned long long ob = (exp_mask & 32) ? (unsigned long long)tile * g.stage

@@ -147,13 +147,16 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threa
     uint32_t threads = ctx->geom_threads;
     if (!threads) {
         const double recs = tile / rec_bytes * 1.03 + 2;       // records a tile owns, with margin
-        threads = ((uint32_t)recs + 31) & ~31u;
+        threads = (((uint32_t)recs + 31) & ~31u) + 32;         // + the scan warp (warp 0 owns no records)
     }
     const uint32_t chunks = (tile + FT_OVL) / 16;
     const uint32_t min_thr = ((chunks + FT_MAXCPT - 1) / FT_MAXCPT + 31) & ~31u;
     if (threads < min_thr) threads = min_thr;
     if (threads < 64) threads = 64;
     if (threads > max_threads) threads = max_threads & ~31u;
+    // a tile may own at most 2 x (threads - 32) records: shrink it for very short records
+    const double fit = 1.8 * (threads - 32) * rec_bytes;
+    if (tile > fit && !ctx->geom_tile) { tile = (uint32_t)fit & ~15u; if (tile < FT_MINTILE) tile = FT_MINTILE; }
     uint32_t stage = ctx->geom_stage;
     if (!stage) stage = (uint32_t)(tile * (1.0 + 48.0 / rec_bytes) + rec_bytes) + 2048;
     stage = (stage + 15) & ~15u;

@@ -310,11 +310,26 @@ def test_fused_tile_geometry_and_fallback(capi):
     with capi.Context() as ctx:
         assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw)
         assert ctx.stats()["fallback_batches"] == 1
-    # (d) tiny records: more lines per tile than the line table holds
-    raw = b"".join(b"@%d\nACACAC\n+\nIIIIII\n" % i for i in range(20000))
+    # (d) tiny records: the tile geometry follows the record size of the batch head ...
+    tiny = b"".join(b"@%d\nACACAC\n+\nIIIIII\n" % i for i in range(20000))
+    with capi.Context(n=2, f=1) as ctx:
+        assert ctx.scan_batch(tiny)[0] == oracle.select_buffer(tiny, n=2, f=1)
+        assert ctx.stats()["fallback_batches"] == 0
+    # ... and when the head misleads it (long records first, then tiny ones: more lines per
+    # tile than the line table holds) the batch takes the generic kernels
+    raw = util.synth_fastq(900, 100, seed=8) + tiny
     with capi.Context(n=2, f=1) as ctx:
         assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, n=2, f=1)
         assert ctx.stats()["fallback_batches"] == 1
+    # records without bases (empty sequence lines) defeat the local record-phase guess of the
+    # fused kernel: '@' / '+' line starts are then ambiguous; results must not change
+    amb = b"".join(b"@r%d\n\n+\n\n" % i if i % 3 else b"@r%d\nACACACACGT\n+\n@@@@@@@@@@\n" % i for i in range(30000))
+    with capi.Context(n=2, f=2) as ctx:
+        assert ctx.scan_batch(amb)[0] == oracle.select_buffer(amb, n=2, f=2)
+    # quality lines that look like headers / separators
+    amb = b"".join(b"@r%d\nACACACACGT\n+\n%s\n" % (i, b"@+@+@+@+@+" if i % 2 else b"+@+@+@+@+@") for i in range(30000))
+    with capi.Context(n=2, f=2) as ctx:
+        assert ctx.scan_batch(amb)[0] == oracle.select_buffer(amb, n=2, f=2)
     # (e) degenerate: newlines only / no newline at all (errors must agree with the oracle)
     good = util.synth_fastq(700, 100, seed=3)
     for raw in (b"\n" * 100000, b"A" * 100000, b"@x\n" + b"A" * 70000 + b"\n+\n" + b"I" * 70000,

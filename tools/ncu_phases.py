@@ -9,9 +9,9 @@ RANGES = {
  'matcher.cuh': [(44,131,'match: bit helpers'),(143,243,'match: encode planes'),(260,357,'match: scan_period'),
                  (359,413,'match: pick winner'),(415,486,'match: match_read_bits'),(488,590,'match: long/dispatch'),(592,640,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
- 'fused.cuh': [(76,98,'tma/mbarrier'),(100,140,'lookback'),(142,150,'index: nl_mask'),(152,174,'block scan'),(185,195,'record lines'),(197,259,'format: copy'),
-               (261,294,'B index chunks'),(296,336,'A stage'),(337,363,'B index fill'),(364,411,'C lookback1+bookkeeping'),(412,450,'D per-record glue'),
-               (451,467,'E offsets'),(468,487,'F format glue + lookback2'),(488,520,'G flush')],
+ 'fused.cuh': [(76,98,'tma/mbarrier'),(100,140,'lookback'),(142,150,'index: nl_mask'),(152,174,'block scan'),(185,195,'record lines'),(197,268,'format: copy'),
+               (270,303,'B index chunks'),(305,345,'A stage'),(346,372,'B index fill'),(373,420,'C lookback1+bookkeeping'),(421,459,'D per-record glue'),
+               (460,476,'E offsets'),(477,496,'F format glue + lookback2'),(497,523,'G flush')],
 }
 PRIO = ['matcher.cuh', 'kernels_v1.cuh', 'fused.cuh']
 fname = cols = cur = None; seen = []; stack = defaultdict(dict); inst = {}; samp = {}; thr = {}; stalls = defaultdict(lambda: defaultdict(float))
