@@ -59,7 +59,7 @@ struct bstr_ctx {
     uint32_t geom_tile, geom_threads, geom_stage;   // BSTR_GEOM overrides (0 = automatic)
     int force_wmax;                // BSTR_WMAX: 2, 4 or 8 (0 = from the record size)
     bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
-    cudaStream_t stream;
+    cudaStream_t stream, stream2;  // stream2: second launch stream of bstr_bench_resident
     cudaEvent_t ev[8];
     bstr::DeviceSlot slot;         // used by bstr_scan_batch / bstr_bench_resident
     uint8_t *d_seqs; uint64_t *d_off; size_t cap_seqs, cap_off;   // bstr_match_reads

@@ -336,6 +336,7 @@ void bstr_destroy(bstr_ctx *ctx)
     cudaFree(ctx->d_seqs); cudaFree(ctx->d_off); cudaFree(ctx->d_flush);
     for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     delete (std::mutex *)ctx->lock;
     delete ctx;
 }
