@@ -10,8 +10,8 @@ RANGES = {
                  (359,413,'match: pick winner'),(415,486,'match: match_read_bits'),(488,590,'match: long/dispatch'),(592,640,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
  'fused.cuh': [(76,98,'tma/mbarrier'),(100,140,'lookback'),(142,150,'index: nl_mask'),(152,174,'block scan'),(185,195,'record lines'),(197,268,'format: copy'),
-               (270,303,'B index chunks'),(305,345,'A stage'),(346,372,'B index fill'),(373,420,'C lookback1+bookkeeping'),(421,459,'D per-record glue'),
-               (460,476,'E offsets'),(477,496,'F format glue + lookback2'),(497,523,'G flush')],
+               (270,303,'B index chunks'),(305,345,'A stage'),(346,372,'B index fill'),(373,438,'C record phase + bookkeeping'),(439,487,'D per-record glue'),
+               (488,505,'E offsets'),(506,536,'F format glue + lookback2'),(537,563,'G flush')],
 }
 PRIO = ['matcher.cuh', 'kernels_v1.cuh', 'fused.cuh']
 fname = cols = cur = None; seen = []; stack = defaultdict(dict); inst = {}; samp = {}; thr = {}; stalls = defaultdict(lambda: defaultdict(float))
