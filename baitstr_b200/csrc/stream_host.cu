@@ -19,6 +19,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
 #include <unistd.h>
 #include <zlib.h>
 
@@ -143,7 +144,7 @@ struct Job {
     uint64_t seq;
     int file;
     PinnedBuf buf;            // input (returned to the pool by the device worker)
-    size_t nbytes;
+    size_t off, nbytes;       // the batch is buf.p[off, off + nbytes)
     bool final, file_end, reader_error;
     // filled by the device worker
     int rc, lane;
@@ -164,7 +165,9 @@ struct Pipeline {
     std::vector<int> lane_state;          // 0 free, 1 submitted, 2 collected (writer still reads it)
     bool reader_finished = false, abort = false;
     uint64_t n_jobs = 0;                  // valid once reader_finished
-    double t_read = 0, t_cut = 0, t_alloc = 0, t_bufwait = 0;   // reader thread, ms (BSTR_TRACE)
+    int n_readers = 4;                    // threads that read one plain file in parallel segments
+    double t_read = 0, t_cut = 0, t_alloc = 0, t_bufwait = 0;   // reader threads, ms, summed (BSTR_TRACE)
+    bool abort_seen() { std::lock_guard<std::mutex> g(mu); return abort; }
 };
 
 static PinnedBuf get_buf(Pipeline &P)
@@ -219,6 +222,115 @@ static void reader_fail(Pipeline &P, int file, PinnedBuf b, const char *what, co
     emit(P, j);
 }
 
+// ---- plain files: several threads read fixed-size segments of the file at once ---------------
+// A segment lands HEAD bytes into its page-locked buffer, its newlines are counted by the
+// thread that read it, and the segments are stitched in file order: the running line count
+// tells where the last whole record of a segment ends (ordinal of the newline a multiple of
+// four), the bytes after it are carried in front of the next segment (that is what HEAD is
+// for).  Batches therefore still start and end on record boundaries and the host still never
+// looks at anything but '\n'.
+struct Segment {
+    PinnedBuf buf;
+    size_t len;
+    uint64_t lines;
+    bool ready, failed;
+};
+
+static bool read_plain_parallel(Pipeline &P, int fi, int fd, uint64_t fsize)
+{
+    const size_t HEAD = 1u << 20, S = P.buf_cap - HEAD;
+    const uint64_t nseg = (fsize + S - 1) / S;
+    std::vector<Segment> segs((size_t)nseg);
+    for (auto &g : segs) { g.buf = PinnedBuf{nullptr, 0}; g.len = 0; g.lines = 0; g.ready = g.failed = false; }
+    std::mutex mu;
+    uint64_t next = 0, frontier = 0, lines = 0;
+    std::vector<uint8_t> tail;
+    bool stop = false;
+
+    auto advance = [&]() {                               // mu held
+        while (frontier < nseg && segs[(size_t)frontier].ready && !stop) {
+            Segment &g = segs[(size_t)frontier];
+            const bool lastseg = frontier + 1 == nseg;
+            if (g.failed) { reader_fail(P, fi, g.buf, "read error on", P.paths[fi]); g.buf.p = nullptr; stop = true; break; }
+            uint8_t *seg = g.buf.p + HEAD;
+            const uint64_t total = lines + g.lines;
+            size_t cut = 0;
+            if (lastseg) cut = g.len;
+            else if (total - (total & 3) > lines) {      // a record ends inside this segment
+                const uint8_t *q = (const uint8_t *)memrchr(seg, '\n', g.len);
+                for (uint64_t d = total & 3; d; d--) q = (const uint8_t *)memrchr(seg, '\n', (size_t)(q - seg));
+                cut = (size_t)(q - seg) + 1;
+            }
+            if (cut == 0 && !lastseg) {                  // no record boundary in here: all of it is carried
+                tail.insert(tail.end(), seg, seg + g.len);
+                put_buf(P, g.buf);
+            } else {
+                std::vector<uint8_t> carry(seg + cut, seg + g.len);
+                Job *j;
+                if (tail.size() <= HEAD) {
+                    memcpy(seg - tail.size(), tail.data(), tail.size());
+                    j = new_job(fi, g.buf, tail.size() + cut, lastseg, lastseg);
+                    j->off = HEAD - tail.size();
+                } else {                                 // a record longer than HEAD: one-off buffer
+                    PinnedBuf big{nullptr, tail.size() + cut + 1};
+                    if (big.cap > (2ull << 30) || cudaHostAlloc((void **)&big.p, big.cap, cudaHostAllocDefault) != cudaSuccess) {
+                        cudaGetLastError(); errno = ENOMEM;
+                        reader_fail(P, fi, g.buf, "record too large reading", P.paths[fi]); g.buf.p = nullptr; stop = true; break;
+                    }
+                    memcpy(big.p, tail.data(), tail.size());
+                    memcpy(big.p + tail.size(), seg, cut);
+                    put_buf(P, g.buf);
+                    j = new_job(fi, big, tail.size() + cut, lastseg, lastseg);
+                }
+                emit(P, j);
+                tail.swap(carry);
+            }
+            g.buf.p = nullptr;
+            lines = total;
+            frontier++;
+        }
+    };
+
+    auto worker = [&]() {
+        cudaSetDevice(P.ctx->dev);
+        for (;;) {
+            PinnedBuf b = get_buf(P);                    // buffer first: the lowest unread segment always has one
+            uint64_t k;
+            {
+                std::lock_guard<std::mutex> g(mu);
+                if (!b.p) { if (!P.abort_seen()) { errno = ENOMEM; reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); } stop = true; return; }
+                if (stop || next >= nseg) { put_buf(P, b); return; }
+                k = next++;
+            }
+            const uint64_t off = k * S;
+            const size_t want = (size_t)(fsize - off < S ? fsize - off : S);
+            size_t have = 0;
+            bool failed = false;
+            const double t0 = now_ms();
+            while (have < want) {
+                ssize_t r = pread(fd, b.p + HEAD + have, want - have, (off_t)(off + have));
+                if (r < 0 && errno == EINTR) continue;
+                if (r < 0) { failed = true; break; }
+                if (r == 0) break;                       // file shrank: what is there is the segment
+                have += (size_t)r;
+            }
+            const double t1 = now_ms();
+            const uint64_t nl = count_newlines(b.p + HEAD, have);
+            const double t2 = now_ms();
+            std::lock_guard<std::mutex> g(mu);
+            P.t_read += t1 - t0; P.t_cut += t2 - t1;
+            Segment &sg = segs[(size_t)k];
+            sg.buf = b; sg.len = have; sg.lines = nl; sg.failed = failed; sg.ready = true;
+            advance();
+        }
+    };
+    std::vector<std::thread> th;
+    for (int i = 0; i < P.n_readers; i++) th.emplace_back(worker);
+    for (auto &t : th) t.join();
+    for (auto &g : segs) if (g.buf.p) put_buf(P, g.buf);     // aborted run
+    return !stop && !P.abort_seen();
+}
+
 static void reader_main(Pipeline *pp)
 {
     Pipeline &P = *pp;
@@ -227,6 +339,14 @@ static void reader_main(Pipeline *pp)
         Source src;
         errno = 0;
         if (src.open_path(P.paths[fi]) != 0) { reader_fail(P, fi, PinnedBuf{nullptr, 0}, "cannot open", P.paths[fi]); break; }
+        struct stat sb;
+        if (!src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && fstat(src.fd, &sb) == 0 && S_ISREG(sb.st_mode) &&
+            (uint64_t)sb.st_size > P.buf_cap) {
+            const bool ok = read_plain_parallel(P, fi, src.fd, (uint64_t)sb.st_size);
+            src.close_all();
+            if (!ok) break;
+            continue;
+        }
         PinnedBuf b = get_buf(P);
         size_t have = 0;
         bool eof = false, stop = false;
@@ -337,7 +457,7 @@ static void device_main(Pipeline *pp, int d)
                 publish(P, job);
                 continue;
             }
-            const int rc = lane_submit(ctx, ctx->lanes[lane], job->buf.p, job->nbytes, job->final ? 1 : 0);
+            const int rc = lane_submit(ctx, ctx->lanes[lane], job->buf.p + job->off, job->nbytes, job->final ? 1 : 0);
             if (rc) {
                 job->rc = rc;
                 { std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock); snprintf(job->msg, sizeof(job->msg), "%s", ctx->err); }
@@ -380,7 +500,8 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     Pipeline P;
     P.ctx = ctx; P.paths = paths; P.npaths = npaths;
     P.buf_cap = ctx->p.batch_bytes;
-    P.bufs_max = (size_t)ctx->n_lanes + 2;
+    P.n_readers = ctx->p.host_threads > 4 ? (ctx->p.host_threads > 16 ? 16 : ctx->p.host_threads) : 4;
+    P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)P.n_readers;
     P.lane_state.assign((size_t)ctx->n_lanes, 0);
     for (auto &b : ctx->engine->pool) {
         if (b.cap == P.buf_cap && P.bufs_made < P.bufs_max) { P.free_bufs.push_back(b); P.bufs_made++; }

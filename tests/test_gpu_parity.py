@@ -413,3 +413,26 @@ def test_run_files_edge_files_and_errors(capi, tmp_path):
             ctx.run_files([pa, str(tmp_path / "nope.fq")], out_fd=fo.fileno(), err_fd=-1)
         assert ei.value.code == -4
     assert open(outp, "rb").read() == oracle.select_buffer(a[:-1])
+
+
+def test_run_files_parallel_segment_reader(capi, tmp_path):
+    """Plain files larger than a batch are read by several threads in fixed segments that are
+    stitched at record boundaries (stream_host.cu: read_plain_parallel): same bytes as the
+    oracle, with a record far longer than the 1 MiB carry area and a file that does not end
+    in a newline."""
+    a = util.synth_fastq(60000, 100, seed=71, tag="p")                    # ~13 MB
+    big = "ACGT" * 700000 + "CAG" * 12 + "TTGACCA" * 300000               # one 4.9 Mbase read
+    rec = ("@huge\n%s\n+\n%s\n" % (big, "I" * len(big))).encode()
+    b = util.synth_fastq(20000, 150, seed=72, tag="q", vary_len=True)
+    p1, p2 = str(tmp_path / "seg1.fq"), str(tmp_path / "seg2.fq")
+    open(p1, "wb").write(a)
+    open(p2, "wb").write((b + rec + b)[:-1])
+    want = oracle.select_buffer(a) + oracle.select_buffer((b + rec + b)[:-1])
+    for threads in (0, 7):
+        outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+        with capi.Context(batch_bytes=4 << 20, host_threads=threads) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            ctx.run_files([p1, p2], out_fd=fo.fileno(), err_fd=fe.fileno())
+            st = ctx.stats()
+        assert open(outp, "rb").read() == want
+        assert open(errp).read() == "Done processing %s\nDone processing %s\n" % (p1, p2)
+        assert st["records"] == 60000 + 40001 and st["batches"] >= 6
