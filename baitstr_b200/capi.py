@@ -49,7 +49,7 @@ class BenchOut(C.Structure):
 EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "bstr_scan_batch",
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
-           "bstr_submit_batch", "bstr_collect_batch"]
+           "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip"]
 
 _lib = None
 
@@ -101,12 +101,26 @@ def load_library():
     lib.bstr_reset_stats.restype = None
     lib.bstr_device_count.argtypes = []
     lib.bstr_device_count.restype = C.c_int
+    lib.bstr_gunzip.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
+    lib.bstr_gunzip.restype = C.c_int
     _lib = lib
     return lib
 
 
 def device_count():
     return load_library().bstr_device_count()
+
+
+def gunzip(path, out_fd=-1, threads=4, range_bytes=1 << 20, seg_bytes=8 << 20):
+    """bstr_gunzip: inflate `path` with the parallel inflater of the ingest side (host only).
+    Returns the stats dict; raises BstrError (not gzip / corrupt / CRC mismatch / truncated)."""
+    lib = load_library()
+    st = (C.c_uint64 * 6)()
+    err = C.create_string_buffer(512)
+    rc = lib.bstr_gunzip(os.fsencode(path), out_fd, threads, range_bytes, seg_bytes, st, err, len(err))
+    if rc != 0:
+        raise BstrError(rc, err.value.decode("latin-1"))
+    return dict(zip(("in_bytes", "out_bytes", "ranges", "accepted", "redone", "members"), [int(x) for x in st]))
 
 
 def kmask_of(ks):

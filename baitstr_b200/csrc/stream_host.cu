@@ -19,10 +19,12 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 #include <zlib.h>
 
+#include <atomic>
 #include <condition_variable>
 #include <deque>
 #include <map>
@@ -33,6 +35,7 @@
 #include <chrono>
 
 #include "host_common.h"
+#include "pinflate.h"
 
 namespace bstr {
 
@@ -165,7 +168,9 @@ struct Pipeline {
     std::vector<int> lane_state;          // 0 free, 1 submitted, 2 collected (writer still reads it)
     bool reader_finished = false, abort = false;
     uint64_t n_jobs = 0;                  // valid once reader_finished
-    int n_readers = 4;                    // threads that read one plain file in parallel segments
+    int n_readers = 4;                    // host threads the caller allows (bstr_params.host_threads, at least 4)
+    int plain_readers = 4;                // threads that read one plain file in parallel segments
+    int gz_decoders = 4, gz_fillers = 2, gz_pending = 3;   // parallel inflate: decoder threads, segment producers, segments decoded ahead
     double t_read = 0, t_cut = 0, t_alloc = 0, t_bufwait = 0;   // reader threads, ms, summed (BSTR_TRACE)
     bool abort_seen() { std::lock_guard<std::mutex> g(mu); return abort; }
 };
@@ -214,44 +219,120 @@ static Job *new_job(int file, PinnedBuf b, size_t nbytes, bool final, bool file_
     return j;
 }
 
-static void reader_fail(Pipeline &P, int file, PinnedBuf b, const char *what, const char *path)
+static void reader_fail(Pipeline &P, int file, PinnedBuf b, const char *what, const char *path, const char *detail = nullptr)
 {
     Job *j = new_job(file, b, 0, true, true);
     j->reader_error = true; j->rc = BSTR_ERR_IO;
-    snprintf(j->msg, sizeof(j->msg), "%s %s: %s", what, path, errno ? strerror(errno) : "I/O error");
+    snprintf(j->msg, sizeof(j->msg), "%s %s: %s", what, path, detail ? detail : errno ? strerror(errno) : "I/O error");
     emit(P, j);
 }
 
-// ---- plain files: several threads read fixed-size segments of the file at once ---------------
+// ---- large files: several threads produce fixed-size segments of the (inflated) file at once ----
 // A segment lands HEAD bytes into its page-locked buffer, its newlines are counted by the
-// thread that read it, and the segments are stitched in file order: the running line count
+// thread that produced it, and the segments are stitched in file order: the running line count
 // tells where the last whole record of a segment ends (ordinal of the newline a multiple of
 // four), the bytes after it are carried in front of the next segment (that is what HEAD is
 // for).  Batches therefore still start and end on record boundaries and the host still never
-// looks at anything but '\n'.
+// looks at anything but '\n'.  Where the segments come from is a SegmentSource: pread() for a
+// plain file, the parallel inflater (pinflate.h) for a .gz file.
+struct SegmentSource {
+    virtual ~SegmentSource() {}
+    // next segment in file order: index, -1 after the last, -2 on error.  Thread-safe; may block.
+    virtual long claim(uint64_t *off, size_t *len, bool *last) = 0;
+    // produce it at dst; *have = bytes written (<= len), *newlines = '\n' among them
+    virtual bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) = 0;
+    virtual bool fold(const pinflate::SegmentInfo &, bool) { return true; }   // called in segment order
+    virtual void cancel() {}
+    virtual const char *error() { return nullptr; }
+    size_t seg_bytes = 0;
+};
+
+struct PlainSource : SegmentSource {
+    int fd; uint64_t fsize, nseg; std::atomic<uint64_t> next{0};
+    PlainSource(int fd_, uint64_t fsize_, size_t S) : fd(fd_), fsize(fsize_), nseg((fsize_ + S - 1) / S) { seg_bytes = S; }
+    long claim(uint64_t *off, size_t *len, bool *last) override
+    {
+        const uint64_t k = next.fetch_add(1);
+        if (k >= nseg) return -1;
+        *off = k * seg_bytes;
+        *len = (size_t)(fsize - *off < seg_bytes ? fsize - *off : seg_bytes);
+        *last = k + 1 == nseg;
+        return (long)k;
+    }
+    bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *) override
+    {
+        size_t got = 0;
+        while (got < len) {
+            ssize_t r = pread(fd, dst + got, len - got, (off_t)(off + got));
+            if (r < 0 && errno == EINTR) continue;
+            if (r < 0) return false;
+            if (r == 0) break;                           // file shrank: what is there is the segment
+            got += (size_t)r;
+        }
+        *have = got;
+        *newlines = count_newlines(dst, got);
+        return true;
+    }
+};
+
+struct GzipSource : SegmentSource {
+    pinflate::Stream z;
+    const uint8_t *map = nullptr; size_t map_size = 0;
+    ~GzipSource() override { z.close(); if (map) munmap((void *)map, map_size); }
+    bool open(int fd, size_t size, int threads, size_t S, int pending)
+    {
+        void *m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m == MAP_FAILED) return false;
+        map = (const uint8_t *)m; map_size = size; seg_bytes = S;
+        madvise(m, size, MADV_SEQUENTIAL);
+        return z.open(map, size, threads, (size_t)1 << 20, S, pending);
+    }
+    long claim(uint64_t *off, size_t *len, bool *last) override { return z.claim(off, len, last); }
+    bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) override
+    {
+        if (!z.fill(off, len, dst, info)) return false;
+        *have = len; *newlines = info->newlines;
+        return true;
+    }
+    bool fold(const pinflate::SegmentInfo &info, bool last) override { return z.fold(info, last); }
+    void cancel() override { z.cancel(); }
+    const char *error() override { return z.error(); }
+};
+
 struct Segment {
     PinnedBuf buf;
     size_t len;
     uint64_t lines;
-    bool ready, failed;
+    bool failed, last;
+    pinflate::SegmentInfo info;
 };
 
-static bool read_plain_parallel(Pipeline &P, int fi, int fd, uint64_t fsize)
+static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int nthreads)
 {
-    const size_t HEAD = 1u << 20, S = P.buf_cap - HEAD;
-    const uint64_t nseg = (fsize + S - 1) / S;
-    std::vector<Segment> segs((size_t)nseg);
-    for (auto &g : segs) { g.buf = PinnedBuf{nullptr, 0}; g.len = 0; g.lines = 0; g.ready = g.failed = false; }
+    const size_t HEAD = 1u << 20;
+    std::map<long, Segment> segs;
     std::mutex mu;
-    uint64_t next = 0, frontier = 0, lines = 0;
+    long frontier = 0;
+    uint64_t lines = 0;
     std::vector<uint8_t> tail;
     bool stop = false;
 
+    auto fail = [&](PinnedBuf b, const char *what) {      // mu held
+        const char *detail = src.error();
+        if (detail && *detail) errno = 0;
+        reader_fail(P, fi, b, what, P.paths[fi], detail && *detail ? detail : nullptr);
+        stop = true;
+        src.cancel();
+    };
     auto advance = [&]() {                               // mu held
-        while (frontier < nseg && segs[(size_t)frontier].ready && !stop) {
-            Segment &g = segs[(size_t)frontier];
-            const bool lastseg = frontier + 1 == nseg;
-            if (g.failed) { reader_fail(P, fi, g.buf, "read error on", P.paths[fi]); g.buf.p = nullptr; stop = true; break; }
+        while (!stop) {
+            auto it = segs.find(frontier);
+            if (it == segs.end()) break;
+            Segment g = std::move(it->second);
+            segs.erase(it);
+            const bool lastseg = g.last;
+            if (g.failed) { fail(g.buf, "read error on"); break; }
+            if (!src.fold(g.info, lastseg)) { fail(g.buf, "read error on"); break; }
             uint8_t *seg = g.buf.p + HEAD;
             const uint64_t total = lines + g.lines;
             size_t cut = 0;
@@ -275,7 +356,7 @@ static bool read_plain_parallel(Pipeline &P, int fi, int fd, uint64_t fsize)
                     PinnedBuf big{nullptr, tail.size() + cut + 1};
                     if (big.cap > (2ull << 30) || cudaHostAlloc((void **)&big.p, big.cap, cudaHostAllocDefault) != cudaSuccess) {
                         cudaGetLastError(); errno = ENOMEM;
-                        reader_fail(P, fi, g.buf, "record too large reading", P.paths[fi]); g.buf.p = nullptr; stop = true; break;
+                        fail(g.buf, "record too large reading"); break;
                     }
                     memcpy(big.p, tail.data(), tail.size());
                     memcpy(big.p + tail.size(), seg, cut);
@@ -285,7 +366,6 @@ static bool read_plain_parallel(Pipeline &P, int fi, int fd, uint64_t fsize)
                 emit(P, j);
                 tail.swap(carry);
             }
-            g.buf.p = nullptr;
             lines = total;
             frontier++;
         }
@@ -294,40 +374,35 @@ static bool read_plain_parallel(Pipeline &P, int fi, int fd, uint64_t fsize)
     auto worker = [&]() {
         cudaSetDevice(P.ctx->dev);
         for (;;) {
-            PinnedBuf b = get_buf(P);                    // buffer first: the lowest unread segment always has one
-            uint64_t k;
+            PinnedBuf b = get_buf(P);                    // buffer first: the lowest unproduced segment always has one
             {
                 std::lock_guard<std::mutex> g(mu);
-                if (!b.p) { if (!P.abort_seen()) { errno = ENOMEM; reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); } stop = true; return; }
-                if (stop || next >= nseg) { put_buf(P, b); return; }
-                k = next++;
+                if (!b.p) { if (!P.abort_seen() && !stop) { errno = ENOMEM; fail(b, "out of page-locked memory reading"); } stop = true; src.cancel(); return; }
+                if (stop) { put_buf(P, b); return; }
             }
-            const uint64_t off = k * S;
-            const size_t want = (size_t)(fsize - off < S ? fsize - off : S);
-            size_t have = 0;
-            bool failed = false;
+            uint64_t off = 0; size_t len = 0; bool last = false;
+            const long k = src.claim(&off, &len, &last);
+            if (k == -1) { put_buf(P, b); return; }
+            if (k < 0) {
+                std::lock_guard<std::mutex> g(mu);
+                if (!stop && !P.abort_seen()) fail(b, "read error on"); else put_buf(P, b);
+                return;
+            }
+            Segment sg;
+            sg.buf = b; sg.len = 0; sg.lines = 0; sg.last = last;
             const double t0 = now_ms();
-            while (have < want) {
-                ssize_t r = pread(fd, b.p + HEAD + have, want - have, (off_t)(off + have));
-                if (r < 0 && errno == EINTR) continue;
-                if (r < 0) { failed = true; break; }
-                if (r == 0) break;                       // file shrank: what is there is the segment
-                have += (size_t)r;
-            }
+            sg.failed = !src.fill(off, len, b.p + HEAD, &sg.len, &sg.lines, &sg.info);
             const double t1 = now_ms();
-            const uint64_t nl = count_newlines(b.p + HEAD, have);
-            const double t2 = now_ms();
             std::lock_guard<std::mutex> g(mu);
-            P.t_read += t1 - t0; P.t_cut += t2 - t1;
-            Segment &sg = segs[(size_t)k];
-            sg.buf = b; sg.len = have; sg.lines = nl; sg.failed = failed; sg.ready = true;
+            P.t_read += t1 - t0;
+            segs[k] = std::move(sg);
             advance();
         }
     };
     std::vector<std::thread> th;
-    for (int i = 0; i < P.n_readers; i++) th.emplace_back(worker);
+    for (int i = 0; i < nthreads; i++) th.emplace_back(worker);
     for (auto &t : th) t.join();
-    for (auto &g : segs) if (g.buf.p) put_buf(P, g.buf);     // aborted run
+    for (auto &kv : segs) if (kv.second.buf.p) put_buf(P, kv.second.buf);     // aborted run
     return !stop && !P.abort_seen();
 }
 
@@ -342,10 +417,36 @@ static void reader_main(Pipeline *pp)
         struct stat sb;
         if (!src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && fstat(src.fd, &sb) == 0 && S_ISREG(sb.st_mode) &&
             (uint64_t)sb.st_size > P.buf_cap) {
-            const bool ok = read_plain_parallel(P, fi, src.fd, (uint64_t)sb.st_size);
+            PlainSource ps(src.fd, (uint64_t)sb.st_size, P.buf_cap - (1u << 20));
+            const bool ok = read_segments_parallel(P, fi, ps, P.plain_readers);
             src.close_all();
             if (!ok) break;
             continue;
+        }
+        if (src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && !getenv("BSTR_SERIAL_INFLATE")) {
+            // a regular .gz file of some size: inflate it on all reader threads (pinflate.h)
+            const int fd = open(P.paths[fi], O_RDONLY);
+            bool done = false, ok = true;
+            if (fd >= 0 && fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size >= (1 << 20)) {
+                GzipSource gs;
+                const size_t S = P.buf_cap - (1u << 20) < ((size_t)32 << 20) ? P.buf_cap - (1u << 20) : (size_t)32 << 20;
+                if (gs.open(fd, (size_t)sb.st_size, P.gz_decoders, S, P.gz_pending)) {
+                    ok = read_segments_parallel(P, fi, gs, P.gz_fillers);
+                    done = true;
+                    if (getenv("BSTR_TRACE")) {
+                        const pinflate::Stats zs = gs.z.stats();
+                        fprintf(stderr, "[bstr] inflate %s: %.1f MB -> %.1f MB, %llu ranges (%llu decoded again), %llu members | threads: decode %.1f search %.1f redo %.1f idle %.1f ms\n",
+                                P.paths[fi], zs.in_bytes / 1e6, zs.out_bytes / 1e6, (unsigned long long)zs.ranges, (unsigned long long)zs.redone,
+                                (unsigned long long)zs.members, zs.decode_ms, zs.search_ms, zs.redo_ms, zs.wait_ms);
+                    }
+                }
+            }
+            if (fd >= 0) close(fd);
+            if (done) {
+                src.close_all();
+                if (!ok) break;
+                continue;
+            }
         }
         PinnedBuf b = get_buf(P);
         size_t have = 0;
@@ -500,8 +601,13 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     Pipeline P;
     P.ctx = ctx; P.paths = paths; P.npaths = npaths;
     P.buf_cap = ctx->p.batch_bytes;
-    P.n_readers = ctx->p.host_threads > 4 ? (ctx->p.host_threads > 16 ? 16 : ctx->p.host_threads) : 4;
-    P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)P.n_readers;
+    auto knob = [](const char *name, int dflt) { const char *v = getenv(name); return v && atoi(v) > 0 ? atoi(v) : dflt; };
+    P.n_readers = ctx->p.host_threads > 4 ? (ctx->p.host_threads > 32 ? 32 : ctx->p.host_threads) : 4;
+    P.plain_readers = knob("BSTR_PLAIN_READERS", P.n_readers >= 8 ? 8 : 4);  // pread + newline count: memory-bound
+    P.gz_fillers = knob("BSTR_GZ_FILLERS", P.n_readers >= 8 ? 4 : 2);        // resolve markers, CRC-32, newline count
+    P.gz_decoders = knob("BSTR_GZ_DECODERS", P.n_readers - P.gz_fillers);    // together they use the host threads allowed
+    P.gz_pending = knob("BSTR_GZ_PENDING", 6);
+    P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)(P.plain_readers > P.gz_fillers ? P.plain_readers : P.gz_fillers);
     P.lane_state.assign((size_t)ctx->n_lanes, 0);
     for (auto &b : ctx->engine->pool) {
         if (b.cap == P.buf_cap && P.bufs_made < P.bufs_max) { P.free_bufs.push_back(b); P.bufs_made++; }
@@ -579,4 +685,60 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
                 ctx->stats.h2d_ms, ctx->stats.kernel_ms, ctx->stats.d2h_ms, (unsigned long long)ctx->stats.batches);
     if (result) set_error(ctx, "%s", errmsg);
     return result;
+}
+
+// Host-only hook (no GPU needed): inflate one .gz file with the parallel inflater that
+// bstr_run_files uses and write the bytes to out_fd.  Exists so that the ingest side can be
+// tested on its own against gzip/zlib.
+extern "C" int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes, uint64_t seg_bytes,
+                           uint64_t *stats6, char *err, size_t errlen)
+{
+    auto say = [&](const char *m) { if (err && errlen) snprintf(err, errlen, "%s", m); };
+    const int fd = open(path, O_RDONLY);
+    struct stat sb;
+    if (fd < 0 || fstat(fd, &sb) != 0) { say(strerror(errno)); if (fd >= 0) close(fd); return BSTR_ERR_IO; }
+    if (sb.st_size == 0) { close(fd); say("not a gzip file"); return BSTR_ERR_IO; }
+    void *m = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) { say(strerror(errno)); return BSTR_ERR_IO; }
+    int rc = 0;
+    {
+        pinflate::Stream z;
+        if (!z.open((const uint8_t *)m, (size_t)sb.st_size, threads, (size_t)range_bytes, (size_t)seg_bytes, 3)) { say(z.error()); rc = BSTR_ERR_IO; }
+        std::mutex mu;
+        std::map<long, std::pair<std::vector<uint8_t>, std::pair<pinflate::SegmentInfo, bool>>> ready;
+        long next = 0;
+        auto consumer = [&]() {
+            for (;;) {
+                uint64_t off = 0; size_t len = 0; bool last = false;
+                const long k = z.claim(&off, &len, &last);
+                if (k == -1) return;
+                std::vector<uint8_t> buf(k >= 0 ? len : 0);
+                pinflate::SegmentInfo info;
+                const bool ok = k >= 0 && z.fill(off, len, buf.data(), &info);
+                std::lock_guard<std::mutex> g(mu);
+                if (!ok) { if (!rc) { rc = BSTR_ERR_IO; say(z.error()); } z.cancel(); return; }
+                ready[k] = std::make_pair(std::move(buf), std::make_pair(std::move(info), last));
+                for (auto it = ready.find(next); it != ready.end() && !rc; it = ready.find(next)) {
+                    if (!z.fold(it->second.second.first, it->second.second.second)) { rc = BSTR_ERR_IO; say(z.error()); z.cancel(); }
+                    else if (out_fd >= 0 && write_all(out_fd, it->second.first.data(), it->second.first.size()) != 0) { rc = BSTR_ERR_IO; say(strerror(errno)); z.cancel(); }
+                    ready.erase(it);
+                    next++;
+                }
+                if (rc) return;
+            }
+        };
+        if (!rc) {
+            std::vector<std::thread> th;
+            for (int i = 0; i < (threads > 3 ? 3 : 2); i++) th.emplace_back(consumer);
+            for (auto &t : th) t.join();
+        }
+        if (stats6) {
+            const pinflate::Stats zs = z.stats();
+            stats6[0] = zs.in_bytes; stats6[1] = zs.out_bytes; stats6[2] = zs.ranges; stats6[3] = zs.accepted; stats6[4] = zs.redone; stats6[5] = zs.members;
+        }
+        z.close();
+    }
+    munmap(m, (size_t)sb.st_size);
+    return rc;
 }

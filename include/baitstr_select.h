@@ -56,7 +56,7 @@ typedef struct bstr_params {
     int32_t host_threads;    /* reader/inflate threads hint (from -p); 0 => default          */
     int32_t want_results;    /* bstr_scan_batch also returns the 16-byte per-read records    */
     int32_t reserved0;
-    uint64_t batch_bytes;    /* raw FASTQ bytes per device batch; 0 => default (64 MiB)      */
+    uint64_t batch_bytes;    /* raw FASTQ bytes per device batch; 0 => default (16 MiB)      */
 } bstr_params;
 
 /* 16 bytes per input record, in input order. fck == 0 <=> read not selected.
@@ -149,6 +149,17 @@ void bstr_host_free(void *p);
 
 void bstr_get_stats(const bstr_ctx *ctx, bstr_stats *st);
 void bstr_reset_stats(bstr_ctx *ctx);
+
+/* Host-only test hook for the ingest side (no GPU needed): inflate the gzip file `path`
+ * (single- or multi-member, bgzip included) on `threads` threads with the parallel inflater
+ * that bstr_run_files uses for "*.gz" inputs (the reference inflates on one thread through
+ * Python's gzip module, src/fastq.pyx:50-51) and write the bytes to out_fd (-1: discard).
+ * range_bytes: compressed bytes per decoder work item; seg_bytes: inflated bytes per output
+ * segment.  stats6 (may be NULL): in bytes, out bytes, ranges searched, runs accepted, runs
+ * decoded again from the true position, gzip members.  0, or BSTR_ERR_IO with a message in err
+ * (not gzip, corrupt deflate data, CRC-32/ISIZE mismatch, truncated file). */
+int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes, uint64_t seg_bytes,
+                uint64_t *stats6, char *err, size_t errlen);
 
 /* number of CUDA devices visible (0 if none / no driver) */
 int bstr_device_count(void);

@@ -436,3 +436,47 @@ def test_run_files_parallel_segment_reader(capi, tmp_path):
         assert open(outp, "rb").read() == want
         assert open(errp).read() == "Done processing %s\nDone processing %s\n" % (p1, p2)
         assert st["records"] == 60000 + 40001 and st["batches"] >= 6
+
+
+def test_run_files_parallel_inflate(capi, tmp_path):
+    """'*.gz' inputs of some size are inflated on several threads (pinflate.cpp) and fed to the GPU
+    in segments stitched at record boundaries: same bytes as the oracle for a single-member file,
+    a bgzip-style multi-member file and a plain concatenation; a truncated and a corrupted file
+    fail with an I/O error."""
+    import struct, zlib
+    a = util.synth_fastq(60000, 100, seed=81, tag="g")                    # ~13 MB
+    b = util.synth_fastq(30000, 150, seed=82, tag="h", vary_len=True)
+    def bgzf(data):
+        out = []
+        for i in range(0, len(data), 65280):
+            blk = data[i:i + 65280]
+            c = zlib.compressobj(6, zlib.DEFLATED, -15)
+            d = c.compress(blk) + c.flush()
+            out.append(b"\x1f\x8b\x08\x04\0\0\0\0\0\xff\x06\0BC\x02\0" + struct.pack("<H", len(d) + 25) + d + struct.pack("<II", zlib.crc32(blk), len(blk)))
+        return b"".join(out) + bytes.fromhex("1f8b08040000000000ff0600424302001b0003000000000000000000")
+    files = {"one.fq.gz": (gzip.compress(a, 6), a), "bg.fq.gz": (bgzf(b), b),
+             "cat.fq.gz": (gzip.compress(b[:len(b) // 2], 1) + gzip.compress(b[len(b) // 2:], 9), b)}
+    paths, want = [], b""
+    for name, (z, raw) in files.items():
+        assert len(z) > (1 << 20)
+        p = str(tmp_path / name)
+        open(p, "wb").write(z)
+        paths.append(p)
+        want += oracle.select_buffer(raw)
+    for threads in (0, 6):
+        outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+        with capi.Context(batch_bytes=4 << 20, host_threads=threads) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            ctx.run_files(paths, out_fd=fo.fileno(), err_fd=fe.fileno())
+            st = ctx.stats()
+        assert open(outp, "rb").read() == want
+        assert open(errp).read() == "".join("Done processing %s\n" % p for p in paths)
+        assert st["records"] == 60000 + 2 * 30000
+    z = files["one.fq.gz"][0]
+    flipped = bytearray(z); flipped[len(z) // 2] ^= 0x40
+    for bad in (z[:len(z) * 2 // 3], bytes(flipped)):
+        p = str(tmp_path / "bad.fq.gz")
+        open(p, "wb").write(bad)
+        with capi.Context(batch_bytes=4 << 20) as ctx, open(os.devnull, "wb") as dn:
+            with pytest.raises(capi.BstrError) as ei:
+                ctx.run_files([p], out_fd=dn.fileno(), err_fd=dn.fileno())
+            assert ei.value.code == -4 and "bad.fq.gz" in str(ei.value)

@@ -31,11 +31,22 @@ try:
         for _ in range(2):
             t0 = time.perf_counter()
             with open(os.devnull, "wb") as dn:
-                subprocess.run([sys.executable, cli] + files, stdout=dn, stderr=dn, check=True)
+                subprocess.run([sys.executable, cli, "-p", str(os.cpu_count())] + files, stdout=dn, stderr=dn, check=True)
             dt = time.perf_counter() - t0
             best = dt if best is None else min(best, dt)
         res["cli_%s_s" % tag] = round(best, 3)
         res["cli_%s_reads_per_s" % tag] = round(reads / best, 1)
+        with open(os.devnull, "wb") as dn:       # one more run with the library's own breakdown (CUDA start-up excluded)
+            tr = subprocess.run([sys.executable, cli, "-p", str(os.cpu_count())] + files, stdout=dn, stderr=subprocess.PIPE, check=True,
+                                env=dict(os.environ, BSTR_TRACE="1")).stderr.decode()
+        infl = [l[len("[bstr] "):] for l in tr.splitlines() if l.startswith("[bstr] inflate")]
+        if infl:
+            res["inflate_trace"] = infl
+        line = [l for l in tr.splitlines() if l.startswith("[bstr] run_files")]
+        if line:
+            res["run_files_%s_trace" % tag] = line[0][len("[bstr] "):]
+            ms = float(line[0].split()[2])
+            res["run_files_%s_reads_per_s" % tag] = round(reads / (ms / 1e3), 1)
     # byte-compare against the reference on a prefix
     rh = ref_reads // 2
     small = []
