@@ -14,7 +14,9 @@
 #include <mutex>
 #include <thread>
 
-#if defined(__SSE2__)
+#if defined(__x86_64__)
+#include <immintrin.h>
+#elif defined(__SSE2__)
 #include <emmintrin.h>
 #endif
 
@@ -532,32 +534,96 @@ static uint64_t find_bgzf_member(const uint8_t *in, size_t size, uint64_t from, 
     return UINT64_MAX;
 }
 
-static void resolve_markers(const uint16_t *s, size_t n, const uint8_t *win, uint8_t *d)
+// Symbols to bytes: markers are looked up in the 32 KiB before the run.  Returns the number of '\n' written.
+static uint64_t resolve_markers(const uint16_t *s, size_t n, const uint8_t *win, uint8_t *d)
 {
     size_t i = 0;
+    uint64_t newlines = 0;
 #if defined(__SSE2__)
-    const __m128i hi = _mm_set1_epi16((short)0xff00);
+    const __m128i hi = _mm_set1_epi16((short)0xff00), nl = _mm_set1_epi8('\n');
     for (; i + 16 <= n; i += 16) {
         const __m128i a = _mm_loadu_si128((const __m128i *)(s + i)), b = _mm_loadu_si128((const __m128i *)(s + i + 8));
         if (_mm_movemask_epi8(_mm_cmpeq_epi16(_mm_and_si128(_mm_or_si128(a, b), hi), _mm_setzero_si128())) == 0xffff)
             _mm_storeu_si128((__m128i *)(d + i), _mm_packus_epi16(a, b));
         else
             for (size_t j = i; j < i + 16; j++) d[j] = s[j] < 256 ? (uint8_t)s[j] : win[s[j] & 0x7fff];
+        newlines += (unsigned)__builtin_popcount((unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(d + i)), nl)));
     }
 #endif
-    for (; i < n; i++) d[i] = s[i] < 256 ? (uint8_t)s[i] : win[s[i] & 0x7fff];
+    for (; i < n; i++) { d[i] = s[i] < 256 ? (uint8_t)s[i] : win[s[i] & 0x7fff]; newlines += d[i] == '\n'; }
+    return newlines;
 }
 
-static uint64_t count_byte(const uint8_t *p, size_t n, uint8_t c)
+// CRC-32 (gzip polynomial) by carry-less multiplication: fold 64 bytes per step, then reduce
+// (Gopal et al., "Fast CRC computation for generic polynomials using PCLMULQDQ", Intel 2009;
+// the folding constants are x^(512+-32), x^(128+-32), x^64 mod P and the Barrett pair for the
+// bit-reflected P = 0x1DB710641).  len is a multiple of 16 and >= 64; crc is the raw register.
+#if defined(__x86_64__)
+__attribute__((target("pclmul,sse4.1")))
+static uint32_t crc32_clmul(const uint8_t *buf, size_t len, uint32_t crc)
 {
-    uint64_t total = 0;
-    while (n) {
-        const size_t m = n < 4096 ? n : 4096;
-        uint32_t k = 0;
-        for (size_t i = 0; i < m; i++) k += p[i] == c;
-        total += k; p += m; n -= m;
+    static const uint64_t __attribute__((aligned(16))) k1k2[] = {0x0154442bd4ull, 0x01c6e41596ull};
+    static const uint64_t __attribute__((aligned(16))) k3k4[] = {0x01751997d0ull, 0x00ccaa009eull};
+    static const uint64_t __attribute__((aligned(16))) k5k0[] = {0x0163cd6124ull, 0x0000000000ull};
+    static const uint64_t __attribute__((aligned(16))) poly[] = {0x01db710641ull, 0x01f7011641ull};
+    __m128i x0, x1, x2, x3, x4, x5, x6, x7, x8, y5, y6, y7, y8;
+    x1 = _mm_loadu_si128((const __m128i *)(buf + 0x00));
+    x2 = _mm_loadu_si128((const __m128i *)(buf + 0x10));
+    x3 = _mm_loadu_si128((const __m128i *)(buf + 0x20));
+    x4 = _mm_loadu_si128((const __m128i *)(buf + 0x30));
+    x1 = _mm_xor_si128(x1, _mm_cvtsi32_si128((int)crc));
+    x0 = _mm_load_si128((const __m128i *)k1k2);
+    buf += 64; len -= 64;
+    while (len >= 64) {
+        x5 = _mm_clmulepi64_si128(x1, x0, 0x00); x6 = _mm_clmulepi64_si128(x2, x0, 0x00);
+        x7 = _mm_clmulepi64_si128(x3, x0, 0x00); x8 = _mm_clmulepi64_si128(x4, x0, 0x00);
+        x1 = _mm_clmulepi64_si128(x1, x0, 0x11); x2 = _mm_clmulepi64_si128(x2, x0, 0x11);
+        x3 = _mm_clmulepi64_si128(x3, x0, 0x11); x4 = _mm_clmulepi64_si128(x4, x0, 0x11);
+        y5 = _mm_loadu_si128((const __m128i *)(buf + 0x00)); y6 = _mm_loadu_si128((const __m128i *)(buf + 0x10));
+        y7 = _mm_loadu_si128((const __m128i *)(buf + 0x20)); y8 = _mm_loadu_si128((const __m128i *)(buf + 0x30));
+        x1 = _mm_xor_si128(_mm_xor_si128(x1, x5), y5); x2 = _mm_xor_si128(_mm_xor_si128(x2, x6), y6);
+        x3 = _mm_xor_si128(_mm_xor_si128(x3, x7), y7); x4 = _mm_xor_si128(_mm_xor_si128(x4, x8), y8);
+        buf += 64; len -= 64;
     }
-    return total;
+    x0 = _mm_load_si128((const __m128i *)k3k4);
+    x5 = _mm_clmulepi64_si128(x1, x0, 0x00); x1 = _mm_clmulepi64_si128(x1, x0, 0x11); x1 = _mm_xor_si128(_mm_xor_si128(x1, x2), x5);
+    x5 = _mm_clmulepi64_si128(x1, x0, 0x00); x1 = _mm_clmulepi64_si128(x1, x0, 0x11); x1 = _mm_xor_si128(_mm_xor_si128(x1, x3), x5);
+    x5 = _mm_clmulepi64_si128(x1, x0, 0x00); x1 = _mm_clmulepi64_si128(x1, x0, 0x11); x1 = _mm_xor_si128(_mm_xor_si128(x1, x4), x5);
+    while (len >= 16) {
+        x2 = _mm_loadu_si128((const __m128i *)buf);
+        x5 = _mm_clmulepi64_si128(x1, x0, 0x00); x1 = _mm_clmulepi64_si128(x1, x0, 0x11); x1 = _mm_xor_si128(_mm_xor_si128(x1, x2), x5);
+        buf += 16; len -= 16;
+    }
+    x2 = _mm_clmulepi64_si128(x1, x0, 0x10);
+    x3 = _mm_setr_epi32(~0, 0, ~0, 0);
+    x1 = _mm_srli_si128(x1, 8);
+    x1 = _mm_xor_si128(x1, x2);
+    x0 = _mm_loadl_epi64((const __m128i *)k5k0);
+    x2 = _mm_srli_si128(x1, 4);
+    x1 = _mm_and_si128(x1, x3);
+    x1 = _mm_clmulepi64_si128(x1, x0, 0x00);
+    x1 = _mm_xor_si128(x1, x2);
+    x0 = _mm_load_si128((const __m128i *)poly);
+    x2 = _mm_and_si128(x1, x3);
+    x2 = _mm_clmulepi64_si128(x2, x0, 0x10);
+    x2 = _mm_and_si128(x2, x3);
+    x2 = _mm_clmulepi64_si128(x2, x0, 0x00);
+    x1 = _mm_xor_si128(x1, x2);
+    return (uint32_t)_mm_extract_epi32(x1, 1);
+}
+#endif
+
+static uint32_t fast_crc32(uint32_t crc, const uint8_t *p, size_t n)           // same contract as zlib's crc32_z
+{
+#if defined(__x86_64__)
+    static const bool have = __builtin_cpu_supports("pclmul") && __builtin_cpu_supports("sse4.1");
+    if (have && n >= 80) {
+        const size_t body = n & ~(size_t)15;
+        crc = ~crc32_clmul(p, body, ~crc);
+        p += body; n -= body;
+    }
+#endif
+    return n ? (uint32_t)crc32_z(crc, p, n) : crc;
 }
 
 } // namespace
@@ -812,19 +878,29 @@ bool Stream::fill(uint64_t off, size_t len, uint8_t *dst, SegmentInfo *info)
         if (at != off + len) return false;
         for (const MemberEnd &m : e->ends) if (m.off > off && m.off < off + len) cuts.push_back(m.off);
     }
-    size_t w = 0;
-    for (const Src &s : srcs) { resolve_markers(s.p->sym + s.from, s.count, s.p->window, dst + w); w += s.count; }
-    if (info) {
-        info->newlines = count_byte(dst, len, '\n');
-        info->parts.clear();
-        uint64_t a = off;
-        cuts.push_back(off + len);
-        for (uint64_t c : cuts) {
-            if (c == a) continue;
-            info->parts.push_back(SegmentInfo::Part{c - a, (uint32_t)crc32_z(0, dst + (a - off), (size_t)(c - a))});
-            a = c;
+    // resolve, count newlines and checksum block by block while the bytes are in cache
+    cuts.push_back(off + len);
+    size_t w = 0, ci = 0;
+    uint64_t newlines = 0, part_len = 0;
+    uint32_t crc = 0;
+    if (info) info->parts.clear();
+    for (const Src &s : srcs) {
+        for (size_t done = 0; done < s.count;) {
+            const size_t blk = s.count - done < 65536 ? s.count - done : 65536;
+            newlines += resolve_markers(s.p->sym + s.from + done, blk, s.p->window, dst + w);
+            if (info) {
+                for (size_t a = w; a < w + blk;) {
+                    const size_t c = (size_t)(cuts[ci] - off) < w + blk ? (size_t)(cuts[ci] - off) : w + blk;
+                    crc = fast_crc32(crc, dst + a, c - a);
+                    part_len += c - a;
+                    a = c;
+                    if (off + c == cuts[ci]) { info->parts.push_back(SegmentInfo::Part{part_len, crc}); crc = 0; part_len = 0; ci++; }
+                }
+            }
+            w += blk; done += blk;
         }
     }
+    if (info) info->newlines = newlines;
     {
         std::lock_guard<std::mutex> g(e->mu);
         for (const Src &s : srcs) {

@@ -284,7 +284,7 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
     if (ctx->p.kmask == 0) { delete (std::mutex *)ctx->lock; delete ctx; return fail("bstr_create: no period in 2..6 selected"); }
     if (ctx->p.batch_bytes == 0) {
         const char *bb = getenv("BSTR_BATCH_BYTES");         // tuning knob; the bstr_params field wins
-        ctx->p.batch_bytes = bb && atoll(bb) > 0 ? (uint64_t)atoll(bb) : 16ull << 20;
+        ctx->p.batch_bytes = bb && atoll(bb) > 0 ? (uint64_t)atoll(bb) : 8ull << 20;
     }
     if (ctx->p.batch_bytes > (2ull << 30)) ctx->p.batch_bytes = 2ull << 30;
     if (ctx->p.n_devices <= 0) {

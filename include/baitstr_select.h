@@ -56,7 +56,7 @@ typedef struct bstr_params {
     int32_t host_threads;    /* reader/inflate threads hint (from -p); 0 => default          */
     int32_t want_results;    /* bstr_scan_batch also returns the 16-byte per-read records    */
     int32_t reserved0;
-    uint64_t batch_bytes;    /* raw FASTQ bytes per device batch; 0 => default (16 MiB)      */
+    uint64_t batch_bytes;    /* raw FASTQ bytes per device batch; 0 => default (8 MiB)       */
 } bstr_params;
 
 /* 16 bytes per input record, in input order. fck == 0 <=> read not selected.

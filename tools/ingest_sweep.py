@@ -21,17 +21,14 @@ try:
         subprocess.check_call("gzip -1 -c %s > %s.gz" % (p, p), shell=True)
         gz.append(p + ".gz")
     MB = 1 << 20
-    configs = [("plain", {}), ("plain", {"BSTR_BATCH_BYTES": 32 * MB}), ("plain", {"BSTR_BATCH_BYTES": 16 * MB}),
-               ("plain", {"BSTR_BATCH_BYTES": 16 * MB, "BSTR_PLAIN_READERS": 8}), ("plain", {"BSTR_BATCH_BYTES": 8 * MB}),
-               ("gz", {}), ("gz", {"BSTR_BATCH_BYTES": 32 * MB}), ("gz", {"BSTR_BATCH_BYTES": 16 * MB}),
-               ("gz", {"BSTR_BATCH_BYTES": 16 * MB, "BSTR_GZ_FILLERS": 6}), ("gz", {"BSTR_BATCH_BYTES": 16 * MB, "BSTR_GZ_FILLERS": 8, "BSTR_GZ_PENDING": 8}),
-               ("gz", {"BSTR_BATCH_BYTES": 16 * MB, "BSTR_GZ_DECODERS": 12, "BSTR_GZ_FILLERS": 4, "BSTR_GZ_PENDING": 6}),
-               ("gz", {"BSTR_BATCH_BYTES": 32 * MB, "BSTR_GZ_FILLERS": 6, "BSTR_GZ_PENDING": 6}),
-               ("gz", {"BSTR_SERIAL_INFLATE": 1})]
+    configs = [("plain", {}), ("plain", {"BSTR_BATCH_BYTES": 16 * MB}), ("plain", {"BSTR_BATCH_BYTES": 4 * MB}),
+               ("gz", {}), ("gz", {"BSTR_GZ_DECODERS": 13, "BSTR_GZ_FILLERS": 3}), ("gz", {"BSTR_GZ_DECODERS": 14, "BSTR_GZ_FILLERS": 2}),
+               ("gz", {"BSTR_GZ_DECODERS": 14, "BSTR_GZ_FILLERS": 3}), ("gz", {"BSTR_BATCH_BYTES": 16 * MB}),
+               ("gz", {"BSTR_GZ_PENDING": 3})]
     for kind, env in configs:
         files = plain if kind == "plain" else gz
         e = dict(os.environ, BSTR_TRACE="1", **{k: str(v) for k, v in env.items()})
-        best, trace = None, ""
+        best, trace, infl = None, "", ""
         for _ in range(2):
             t0 = time.perf_counter()
             with open(os.devnull, "wb") as dn:
@@ -40,7 +37,8 @@ try:
             if best is None or dt < best:
                 best = dt
                 trace = [l for l in r.stderr.decode().splitlines() if l.startswith("[bstr] run_files")][0]
-        print("%-5s %-90s wall %.2f s | %s" % (kind, env, best, trace[7:trace.index("| writer")]), flush=True)
+                infl = " ".join(l[l.index("| threads:"):] for l in r.stderr.decode().splitlines() if l.startswith("[bstr] inflate"))
+        print("%-5s %-90s wall %.2f s | %s" % (kind, env, best, trace[7:trace.index("| writer")] + (infl if kind == "gz" else "")), flush=True)
 finally:
     for f in os.listdir(tmp):
         os.unlink(os.path.join(tmp, f))
