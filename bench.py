@@ -259,6 +259,11 @@ def run_ours(args):
             print("bench.py: GPU output differs from the oracle on the sample", file=sys.stderr)
             sys.exit(1)
 
+    # ---- file ingest (host side of bstr_run_files) on a bounded sample: plain and .gz ---------
+    ingest = None
+    if world == 1 and not args.no_ingest:
+        ingest = measure_ingest(args.ingest_reads, local)
+
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": "reads/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
@@ -275,13 +280,50 @@ def run_ours(args):
                 "path": "bstr_submit_batch/bstr_collect_batch, %d lanes, %d sub-batches of %d reads per step "
                         "(pinned host in -> pinned host out)" % (nl, len(jobs), args.e2e_batch_reads)},
         "gpu_launches": res["launches_per_step"] * args.steps,
-        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "ingest": ingest,
         "out_checksum_fnv1a": "%016x" % res["out_checksum"],
     }
     print(json.dumps(line))
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def measure_ingest(nreads, device):
+    """FILES -> bstr_run_files -> /dev/null for a prefix of the workload, as plain FASTQ and as
+    gzip -1 (the C4/C5 input format): what the reader / parallel inflater / stitcher sustain when
+    the GPU is not the limit.  Not part of `value` or `e2e`."""
+    import shutil
+    from baitstr_b200 import capi, synth
+    tmp = tempfile.mkdtemp(prefix="bstr_ingest_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    cores = len(os.sched_getaffinity(0))
+    out = {"reads": nreads, "host_threads": cores, "sink": "/dev/null", "source": "tmpfs, two mate files"}
+    try:
+        plain = []
+        for mate in (1, 2):
+            p = os.path.join(tmp, "m%d.fq" % mate)
+            synth.generate(CFG, READ_LEN, 0, nreads // 2, mate).tofile(p)
+            plain.append(p)
+        procs = [subprocess.Popen("gzip -1 -c %s > %s.gz" % (p, p), shell=True) for p in plain]
+        if any(pr.wait() for pr in procs):
+            raise RuntimeError("gzip failed")
+        ctx = capi.Context(devices=[device], host_threads=cores, **FLAGS)
+        with open(os.devnull, "wb") as dn:
+            for kind, files in (("plain", plain), ("gz", [p + ".gz" for p in plain])):
+                best = None
+                for _ in range(3):                                   # first pass allocates the page-locked buffers
+                    t0 = time.perf_counter()
+                    ctx.run_files(files, out_fd=dn.fileno(), err_fd=dn.fileno())
+                    dt = time.perf_counter() - t0
+                    best = dt if best is None else min(best, dt)
+                out[kind] = {"reads_per_s": round(nreads / best, 1), "file_GB_per_s": round(sum(os.path.getsize(f) for f in files) / best / 1e9, 3),
+                             "ms": round(best * 1e3, 1)}
+        ctx.close()
+    except Exception as e:                                           # never lose the bench line over the side measurement
+        out["error"] = str(e)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
 
 
 def run_reference(args):
@@ -355,6 +397,8 @@ def main():
     ap.add_argument("--batch-reads", type=int, default=BATCH_READS)
     ap.add_argument("--cpu-sample", type=int, default=1_000_000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ingest", action="store_true")
+    ap.add_argument("--ingest-reads", type=int, default=8_000_000)
     ap.add_argument("--e2e-batch-reads", type=int, default=1_000_000)
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     args = ap.parse_args()
