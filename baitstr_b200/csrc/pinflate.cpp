@@ -243,16 +243,47 @@ static bool read_dynamic_header(BitReader &br, Huff &h, bool strict)
 // ---------------------------------------------------------------------------------------------
 struct MemberEnd { uint64_t off; uint32_t crc, isize; };      // off: symbols of this range before the member ended
 
+// Symbol buffers go round: a run takes one that a finished run gave back, so the pages stay
+// mapped and warm instead of being faulted in again for every range.
+struct SymPool {
+    std::mutex mu;
+    std::vector<std::pair<uint16_t *, size_t>> idle;
+    size_t keep = 8;
+    ~SymPool() { for (auto &b : idle) free(b.first); }
+    bool take(uint16_t **p, size_t *cap)
+    {
+        std::lock_guard<std::mutex> g(mu);
+        if (idle.empty()) return false;
+        size_t best = 0;
+        for (size_t i = 1; i < idle.size(); i++) if (idle[i].second > idle[best].second) best = i;
+        *p = idle[best].first; *cap = idle[best].second;
+        idle[best] = idle.back(); idle.pop_back();
+        return true;
+    }
+    void give(uint16_t *p, size_t cap)
+    {
+        if (!p) return;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            if (idle.size() < keep && cap <= ((size_t)64 << 20)) { idle.emplace_back(p, cap); return; }
+        }
+        free(p);
+    }
+};
+
 struct Run {
     uint16_t *sym = nullptr;
     size_t n = 0, cap = 0;
     uint64_t start_bit = 0, end_bit = 0;
     bool stream_end = false;
     std::vector<MemberEnd> ends;
-    ~Run() { free(sym); }
+    SymPool *pool = nullptr;
+    explicit Run(SymPool *p = nullptr) : pool(p) {}
+    ~Run() { if (pool) pool->give(sym, cap); else free(sym); }
     bool reserve(size_t extra)
     {
         if (n + extra <= cap) return true;
+        if (!sym && pool && pool->take(&sym, &cap) && n + extra <= cap) return true;
         size_t nc = cap ? cap + cap / 2 : (size_t)1 << 20;
         while (nc < n + extra) nc += nc / 2;
         uint16_t *p = (uint16_t *)realloc(sym, nc * sizeof(uint16_t));
@@ -638,8 +669,9 @@ struct Piece {                          // an accepted run: inflated bytes [out_
     size_t n = 0;
     uint64_t out_off = 0;
     uint8_t *window = nullptr;          // the 32 KiB before it
-    size_t resolved = 0;
-    ~Piece() { free(sym); free(window); }
+    size_t resolved = 0, cap = 0;
+    SymPool *pool = nullptr;
+    ~Piece() { if (pool) pool->give(sym, cap); else free(sym); free(window); }
 };
 
 struct Range {
@@ -675,7 +707,9 @@ public:
     uint64_t run_len = 0, fold_off = 0;
     size_t next_end = 0;
     Stats st;
+    SymPool pool;
     std::vector<std::thread> threads;
+    ~Engine() { pieces.clear(); ranges.clear(); }        // hand every buffer back while the pool is still alive
 
     bool stopping() const { return ended || failed || quit.load(std::memory_order_relaxed); }
     void fail(const char *msg)
@@ -692,7 +726,7 @@ public:
             p->window = (uint8_t *)malloc(32768);
             if (!p->window) { fail("out of memory"); return; }
             memcpy(p->window, window, 32768);
-            p->sym = run->sym; p->n = run->n; p->out_off = accepted_out;
+            p->sym = run->sym; p->n = run->n; p->cap = run->cap; p->pool = run->pool; p->out_off = accepted_out;
             run->sym = nullptr;
             if (p->n >= 32768) resolve_markers(p->sym + p->n - 32768, 32768, p->window, window);
             else {
@@ -728,7 +762,7 @@ public:
             // nothing usable starts at pos: decode from the known position
             const uint64_t from = pos, stop = (uint64_t)(cur + 1) * C * 8;
             lk.unlock();
-            std::unique_ptr<Run> run(new Run);
+            std::unique_ptr<Run> run(new Run(&pool));
             const double t0 = now_ms();
             const int rc = decode_run(in, size, from, stop, false, soft_cap, *run, quit);
             const double t1 = now_ms();
@@ -744,7 +778,7 @@ public:
         const uint64_t lo = (uint64_t)j * C * 8, hi = (uint64_t)(j + 1) * C * 8 < (uint64_t)size * 8 ? (uint64_t)(j + 1) * C * 8 : (uint64_t)size * 8;
         state = 3;
         if (j == 0) {                                           // the first range starts where the gzip header ends
-            out.reset(new Run);
+            out.reset(new Run(&pool));
             const double t0 = now_ms();
             const int rc = decode_run(in, size, pos0, hi, false, soft_cap, *out, quit);
             t_decode += now_ms() - t0;
@@ -761,7 +795,7 @@ public:
             const double t1 = now_ms();
             t_search += t1 - t0;
             if (c == UINT64_MAX) return;
-            out.reset(new Run);
+            out.reset(new Run(&pool));
             const int rc = decode_run(in, size, c, hi, true, soft_cap, *out, quit);
             t_decode += now_ms() - t1;
             if (rc == D_OK) { state = 2; return; }
@@ -824,6 +858,7 @@ bool Stream::open(const uint8_t *data, size_t size, int threads, size_t range_by
     e->S = seg_bytes < 4096 ? 4096 : seg_bytes;
     e->nthreads = threads < 1 ? 1 : threads;
     e->look = (size_t)e->nthreads * 2 + 2;
+    e->pool.keep = e->look + 8;
     e->limit = (size_t)(pending_segments < 2 ? 2 : pending_segments) * e->S;
     e->soft_cap = e->S > ((size_t)64 << 20) ? e->S : (size_t)64 << 20;
     e->ranges.resize((size + e->C - 1) / e->C);
@@ -905,7 +940,7 @@ bool Stream::fill(uint64_t off, size_t len, uint8_t *dst, SegmentInfo *info)
         std::lock_guard<std::mutex> g(e->mu);
         for (const Src &s : srcs) {
             s.p->resolved += s.count;
-            if (s.p->resolved == s.p->n) { free(s.p->sym); free(s.p->window); s.p->sym = nullptr; s.p->window = nullptr; }
+            if (s.p->resolved == s.p->n) { e->pool.give(s.p->sym, s.p->cap); free(s.p->window); s.p->sym = nullptr; s.p->window = nullptr; }
         }
         while (e->first_live < e->pieces.size() && !e->pieces[e->first_live]->sym) e->first_live++;
         e->filled_out += len;
