@@ -565,8 +565,10 @@ static uint64_t find_bgzf_member(const uint8_t *in, size_t size, uint64_t from, 
     return UINT64_MAX;
 }
 
-// Symbols to bytes: markers are looked up in the 32 KiB before the run.  Returns the number of '\n' written.
-static uint64_t resolve_markers(const uint16_t *s, size_t n, const uint8_t *win, uint8_t *d)
+// Symbols to bytes through `lut` (identity for 0..255, the 32 KiB before the run at 0x8000...: in
+// DNA most bases are copies of copies that lead back into that history, so about half of all
+// symbols are markers and a branch per symbol would mispredict).  Returns the number of '\n' written.
+static uint64_t resolve_markers(const uint16_t *s, size_t n, const uint8_t *lut, uint8_t *d)
 {
     size_t i = 0;
     uint64_t newlines = 0;
@@ -577,11 +579,11 @@ static uint64_t resolve_markers(const uint16_t *s, size_t n, const uint8_t *win,
         if (_mm_movemask_epi8(_mm_cmpeq_epi16(_mm_and_si128(_mm_or_si128(a, b), hi), _mm_setzero_si128())) == 0xffff)
             _mm_storeu_si128((__m128i *)(d + i), _mm_packus_epi16(a, b));
         else
-            for (size_t j = i; j < i + 16; j++) d[j] = s[j] < 256 ? (uint8_t)s[j] : win[s[j] & 0x7fff];
+            for (size_t j = i; j < i + 16; j++) d[j] = lut[s[j]];
         newlines += (unsigned)__builtin_popcount((unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(d + i)), nl)));
     }
 #endif
-    for (; i < n; i++) { d[i] = s[i] < 256 ? (uint8_t)s[i] : win[s[i] & 0x7fff]; newlines += d[i] == '\n'; }
+    for (; i < n; i++) { d[i] = lut[s[i]]; newlines += d[i] == '\n'; }
     return newlines;
 }
 
@@ -668,7 +670,7 @@ struct Piece {                          // an accepted run: inflated bytes [out_
     uint16_t *sym = nullptr;
     size_t n = 0;
     uint64_t out_off = 0;
-    uint8_t *window = nullptr;          // the 32 KiB before it
+    uint8_t *window = nullptr;          // symbol -> byte: 64 KiB table, identity at 0..255, the 32 KiB before the run at 0x8000...
     size_t resolved = 0, cap = 0;
     SymPool *pool = nullptr;
     ~Piece() { if (pool) pool->give(sym, cap); else free(sym); free(window); }
@@ -723,9 +725,10 @@ public:
         for (const MemberEnd &m : run->ends) { ends.push_back(MemberEnd{accepted_out + m.off, m.crc, m.isize}); st.members++; }
         if (run->n) {
             std::unique_ptr<Piece> p(new Piece);
-            p->window = (uint8_t *)malloc(32768);
+            p->window = (uint8_t *)malloc(65536);
             if (!p->window) { fail("out of memory"); return; }
-            memcpy(p->window, window, 32768);
+            for (int v = 0; v < 256; v++) p->window[v] = (uint8_t)v;
+            memcpy(p->window + 0x8000, window, 32768);
             p->sym = run->sym; p->n = run->n; p->cap = run->cap; p->pool = run->pool; p->out_off = accepted_out;
             run->sym = nullptr;
             if (p->n >= 32768) resolve_markers(p->sym + p->n - 32768, 32768, p->window, window);
