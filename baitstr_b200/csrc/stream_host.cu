@@ -604,7 +604,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     auto knob = [](const char *name, int dflt) { const char *v = getenv(name); return v && atoi(v) > 0 ? atoi(v) : dflt; };
     P.n_readers = ctx->p.host_threads > 4 ? (ctx->p.host_threads > 32 ? 32 : ctx->p.host_threads) : 4;
     P.plain_readers = knob("BSTR_PLAIN_READERS", P.n_readers >= 8 ? 8 : 4);  // pread + newline count: memory-bound
-    P.gz_fillers = knob("BSTR_GZ_FILLERS", P.n_readers >= 8 ? 4 : 2);        // resolve markers, CRC-32, newline count
+    P.gz_fillers = knob("BSTR_GZ_FILLERS", P.n_readers >= 8 ? 3 : 2);        // resolve markers, CRC-32, newline count
     P.gz_decoders = knob("BSTR_GZ_DECODERS", P.n_readers - P.gz_fillers);    // together they use the host threads allowed
     P.gz_pending = knob("BSTR_GZ_PENDING", 6);
     P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)(P.plain_readers > P.gz_fillers ? P.plain_readers : P.gz_fillers);

@@ -480,3 +480,27 @@ def test_run_files_parallel_inflate(capi, tmp_path):
             with pytest.raises(capi.BstrError) as ei:
                 ctx.run_files([p], out_fd=dn.fileno(), err_fd=dn.fileno())
             assert ei.value.code == -4 and "bad.fq.gz" in str(ei.value)
+
+
+def test_run_files_parallel_readers_stop_on_bad_record(capi, tmp_path):
+    """A malformed record deep inside a large plain or gz file: the run stops with the FASTQ error
+    of that record (file and 0-based record index in the message), the reader and inflater threads
+    are torn down (no hang), and the context stays usable."""
+    a = util.synth_fastq(90000, 100, seed=91, tag="b")
+    lines = a.split(b"\n")
+    bad_rec = 61234
+    lines[4 * bad_rec + 1] = lines[4 * bad_rec + 1][:40] + b"R" + lines[4 * bad_rec + 1][41:]     # base outside acgtnACGTN.
+    broken = b"\n".join(lines)
+    good = str(tmp_path / "good.fq")
+    open(good, "wb").write(a)
+    with capi.Context(batch_bytes=4 << 20, host_threads=8) as ctx, open(os.devnull, "wb") as dn:
+        for name, data in (("bad.fq", broken), ("bad.fq.gz", gzip.compress(broken, 6))):
+            p = str(tmp_path / name)
+            open(p, "wb").write(data)
+            with pytest.raises(capi.BstrError) as ei:
+                ctx.run_files([good, p, good], out_fd=dn.fileno(), err_fd=dn.fileno())
+            assert ei.value.code == -11 and name in str(ei.value) and "record %d" % bad_rec in str(ei.value), str(ei.value)
+        outp = str(tmp_path / "after.fq")
+        with open(outp, "wb") as fo:
+            ctx.run_files([good], out_fd=fo.fileno(), err_fd=dn.fileno())
+        assert open(outp, "rb").read() == oracle.select_buffer(a)
