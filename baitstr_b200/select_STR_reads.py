@@ -1,13 +1,28 @@
 """Drop-in for the reference's ``select_STR_reads`` extension module.
 
-Same entry point, same 11 positional arguments, same stdout/stderr behaviour as
-/root/reference/src/select_STR_reads.pyx:339-373; the work happens in
-libbaitstr_select.so on the GPU (bstr_run_files).  ``num_processes`` and ``chunksize`` are
-accepted and never change the output (they only size host staging).
+Same module-level names, argument order and return shapes as
+/root/reference/src/select_STR_reads.pyx: ``select_str_reads`` (:339-373, the entry point the
+driver script calls), ``MatchPatternsAndReportBest`` (:106), ``ProcessSequence`` (:294),
+``ReverseComplement`` (:187), ``PrintSequence`` (:171) and the record type ``fastqsequence``
+(src/fastq.pyx:15-19).  The matching happens in libbaitstr_select.so on the GPU; there is no CPU
+path here.  ``num_processes`` and ``chunksize`` are accepted and never change the output (they
+only size host staging); ``debug_flag`` / ``check_strs`` are accepted, their stderr reports are
+not reproduced.
 """
+import re
 import sys
 
 from . import capi
+
+_PATTERN = re.compile(r"^\(\?=\(\(\?=\(\.\{(\d+)\}\)\)\\2\{(\d+),\}\)\)$")      # pyx:350
+_COMPLEMENT = bytes.maketrans(b"atcgnATCGN", b"tagcnTAGCN")                      # pyx:188
+
+
+class fastqsequence(object):
+    """src/fastq.pyx:15-19: name (header without '@'), seq, qual."""
+
+    def __init__(self, name, seq, qual):
+        self.name, self.seq, self.qual = name, seq, qual
 
 
 def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_quals,
@@ -23,15 +38,93 @@ def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_
         ctx.close()
 
 
-def MatchPatternsAndReportBest(string, only_k_mers, remove_homopolymers, flanking_distance,
-                               num_minimum_copies=2, altalgo=True):
-    """Per-strand test hook, the GPU counterpart of select_STR_reads.pyx:106 (batch of one).
-    Returns (motif, copies, start, end) or None for the string as given (one strand)."""
-    with capi.Context(n=num_minimum_copies, f=flanking_distance, ks=only_k_mers,
-                      rmhm=remove_homopolymers, altalgo=altalgo) as ctx:
-        s = string.encode("latin-1") if isinstance(string, str) else bytes(string)
-        fstart, _, fck, _ = (int(x) for x in ctx.match_reads([s])[0])
+def _periods_and_copies(patterns):
+    """The reference passes the regex strings built at pyx:350; plain periods are accepted too
+    (then the minimum copy number is the reference's default, 2)."""
+    ks, n = [], None
+    for p in patterns:
+        if isinstance(p, int):
+            ks.append(p)
+            continue
+        m = _PATTERN.match(p)
+        if not m:
+            raise ValueError("not a select_STR_reads pattern: %r" % (p,))
+        ks.append(int(m.group(1)))
+        if n is not None and n != int(m.group(2)):
+            raise ValueError("patterns disagree on the minimum copy number")
+        n = int(m.group(2))
+    return ks, (2 if n is None else n)
+
+
+_contexts = {}                       # parameter tuple -> capi.Context (per-read hooks are called in loops)
+
+
+def _context(n, f, ks, rmhm, altalgo):
+    key = (n, f, tuple(sorted(ks)), bool(rmhm), bool(altalgo))
+    ctx = _contexts.get(key)
+    if ctx is None:
+        if len(_contexts) >= 8:
+            _contexts.pop(next(iter(_contexts))).close()
+        ctx = _contexts[key] = capi.Context(n=n, f=f, ks=list(key[2]), rmhm=key[3], altalgo=key[4])
+    return ctx
+
+
+def _as_bytes(string):
+    return string.encode("latin-1") if isinstance(string, str) else bytes(string)
+
+
+def _tuple(seq, start, ck, as_str):
+    """(len(STR), copies, STR, motif, start, end): the tuple the reference collects and
+    maximises (pyx:93,101-102 / :149,153)."""
+    k, c = ck & 7, ck >> 3
+    motif, rep = seq[start:start + k], seq[start:start + k * c]
+    if as_str:
+        motif, rep = motif.decode("latin-1"), rep.decode("latin-1")
+    return (k * c, c, rep, motif, start, start + k * c)
+
+
+def ReverseComplement(seq):
+    """pyx:187-189: complement of acgtn/ACGTN, every other byte unchanged, reversed."""
+    if isinstance(seq, str):
+        return seq.encode("latin-1").translate(_COMPLEMENT)[::-1].decode("latin-1")
+    return bytes(seq).translate(_COMPLEMENT)[::-1]
+
+
+def MatchPatternsAndReportBest(string, patterns, remove_homopolymers, flanking_distance,
+                               debug_flag=False, altalgo=True):
+    """pyx:106 (and :58 for altalgo): best (len(STR), copies, STR, motif, start, end) of ONE
+    strand, or None.  The string is taken as given (the reference upper-cases in the reader,
+    src/fastq.pyx:83, not here; its regex is case-insensitive, the tuple keeps the input's
+    case)."""
+    ks, n = _periods_and_copies(patterns)
+    s = _as_bytes(string)
+    ctx = _context(n, flanking_distance, ks, remove_homopolymers, altalgo)
+    fstart, _, fck, _ = (int(x) for x in ctx.match_reads([s])[0])
     if fck == 0:
         return None
-    k, c = fck & 7, fck >> 3
-    return (s[fstart:fstart + k].decode("latin-1").upper(), c, fstart, fstart + k * c)
+    return _tuple(s, fstart, fck, isinstance(string, str))
+
+
+def ProcessSequence(patterns, remove_homopolymers, flanking_distance, debug_flag, altalgo,
+                    to_check, check_strs, illumina_quals, s):
+    """pyx:294-319: None, or (s, match, rc_match) when both strands have a best STR (rc_match in
+    the coordinates of the reverse-complemented sequence)."""
+    if s is None:
+        return None
+    ks, n = _periods_and_copies(patterns)
+    seq = _as_bytes(s.seq)
+    ctx = _context(n, flanking_distance, ks, remove_homopolymers, altalgo)
+    fstart, rstart, fck, rck = (int(x) for x in ctx.match_reads([seq])[0])
+    if fck == 0 or rck == 0:
+        return None
+    as_str = isinstance(s.seq, str)
+    return (s, _tuple(seq, fstart, fck, as_str), _tuple(ReverseComplement(seq), rstart, rck, as_str))
+
+
+def PrintSequence(s, match, rc_match, illumina_quals):
+    """pyx:171-185 (host-side formatter of one record; bstr_run_files formats on the GPU)."""
+    out = sys.stdout
+    out.write("@%s\t%s\t%d\t%d\t%d\t%s\t%d\t%d\t%d\n" % (
+        s.name, match[3], match[1], match[4], match[5], rc_match[3], rc_match[1], rc_match[4], rc_match[5]))
+    out.write("%s\n+\n" % s.seq)
+    out.write("%s\n" % ("".join(chr(ord(x) - 64 + 33) for x in s.qual) if illumina_quals else s.qual))

@@ -504,3 +504,50 @@ def test_run_files_parallel_readers_stop_on_bad_record(capi, tmp_path):
         with open(outp, "wb") as fo:
             ctx.run_files([good], out_fd=fo.fileno(), err_fd=dn.fileno())
         assert open(outp, "rb").read() == oracle.select_buffer(a)
+
+
+def test_module_level_api_reads_like_the_reference(capi, capsys):
+    """baitstr_b200.select_STR_reads mirrors the reference module (select_STR_reads.pyx:106,171,
+    187,294): same call shapes and return tuples, so the reference's own call sites work
+    unchanged.  Checked on the known answers of SURVEY.md 8(a) and, when oracle/_ref is built,
+    against the unmodified reference on random strings."""
+    from baitstr_b200 import select_STR_reads as ours
+    def pats(ks, n):
+        return [r'(?=((?=(.{%d}))\2{%d,}))' % (k, n) for k in ks]
+    K = [2, 3, 4, 5, 6]
+    s = "GGCATATATATCG"
+    assert ours.MatchPatternsAndReportBest(s, pats(K, 2), False, 0, False, True) == (8, 4, "ATATATAT", "AT", 3, 11)
+    assert ours.ReverseComplement("ttacg.NRa") == "tRN.cgtaa"
+    assert ours.MatchPatternsAndReportBest(ours.ReverseComplement(s), pats(K, 2), False, 0, False, True)[3:] == ("AT", 2, 10)
+    assert ours.MatchPatternsAndReportBest("CGTAAAAAAATGC", pats(K, 2), True, 0, False, True) is None
+    assert ours.MatchPatternsAndReportBest("TTAGAGAGAGAGAGAGCTTCATGCATTT", pats(K, 2), False, 8, False, False) is None   # -x
+    assert ours.MatchPatternsAndReportBest("TTACGACGACGTT", pats(K, 3), False, 0, False, True) == (9, 3, "ACGACGACG", "ACG", 2, 11)
+    rec = ours.fastqsequence("r1 x\tcomment", "TTACGTAGACGTAGACGTAGACGTT", "h" * 25)
+    got = ours.ProcessSequence(pats(K, 2), False, 0, False, True, None, None, True, rec)
+    assert got[0] is rec and got[1] == (18, 3, "TAGACG" * 3, "TAGACG", 5, 23) and got[2][3:] == ("TCTACG", 4, 22)
+    assert ours.ProcessSequence(pats(K, 2), False, 5, False, True, None, None, False,
+                                ours.fastqsequence("r2", "AGAGAGAGAGAGCTTCATGCA", "I" * 21)) is None
+    ours.PrintSequence(*got, illumina_quals=True)
+    assert capsys.readouterr().out == "@r1 x\tcomment\tTAGACG\t3\t5\t23\tTCTACG\t3\t4\t22\n%s\n+\n%s\n" % (rec.seq, "I" * 25)
+    try:
+        from oracle.ref_select import load_reference
+        ref = load_reference()
+    except Exception:
+        return
+    rng = random.Random(17)
+    for it in range(150):
+        L = rng.choice([30, 64, 100, 150])
+        alpha = rng.choice(["ACGT", "AC", "ACGTN", "ACGT."])
+        t = "".join(rng.choice(alpha) for _ in range(L))
+        if rng.random() < 0.6:
+            k = rng.randint(2, 6); m = "".join(rng.choice("ACGT") for _ in range(k))
+            p = rng.randint(0, L - 1); rep = (m * 20)[:rng.randint(2 * k, 10 * k)]
+            t = (t[:p] + rep + t[p + len(rep):])[:L]
+        n, f = rng.choice([2, 3]), rng.choice([0, 5, 31])
+        ks = rng.choice([K, [2, 3], [4, 6]])
+        rmhm, alt = rng.random() < 0.3, rng.random() < 0.7
+        for strand in (t, ref.ReverseComplement(t)):
+            want = ref.MatchPatternsAndReportBest(strand, pats(ks, n), rmhm, f, False, alt)
+            got = ours.MatchPatternsAndReportBest(strand, pats(ks, n), rmhm, f, False, alt)
+            assert (got is None) == (want is None) and (got is None or got == (want[0], int(want[1]), want[2], want[3], want[4], want[5])), (strand, ks, n, f, rmhm, alt)
+        assert ours.ReverseComplement(t) == ref.ReverseComplement(t)
