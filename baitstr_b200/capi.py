@@ -13,7 +13,8 @@ ABI_VERSION = 1
 
 
 def library_path():
-    return os.path.join(HERE, "libbaitstr_select.so")
+    # BSTR_LIB: another build of the same library (kernel A/B measurements only)
+    return os.environ.get("BSTR_LIB") or os.path.join(HERE, "libbaitstr_select.so")
 
 
 class Params(C.Structure):

@@ -19,7 +19,13 @@
 
 namespace bstr {
 
-constexpr int FT_MAXTHREADS = 256;            // launch bound; the host picks 64..256 per batch
+#ifndef BSTR_MAXTHREADS
+#define BSTR_MAXTHREADS 256
+#endif
+#ifndef BSTR_MINCTAS
+#define BSTR_MINCTAS 2
+#endif
+constexpr int FT_MAXTHREADS = BSTR_MAXTHREADS;   // launch bound; the host picks 64..FT_MAXTHREADS per batch
 constexpr int FT_MAXCPT = 16;                  // 16-byte chunks per thread in the index phase
 constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
 constexpr int FT_MAXREGION = 65504;            // line positions are 16-bit
@@ -302,7 +308,7 @@ __device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileG
 }
 
 template <int WMAX>
-__global__ void __launch_bounds__(FT_MAXTHREADS, 2)
+__global__ void __launch_bounds__(FT_MAXTHREADS, BSTR_MINCTAS)
 k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
              BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
              unsigned long long *ticket, uint32_t ntiles, ReadResult *res, uint8_t *out,
