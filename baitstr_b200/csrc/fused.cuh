@@ -27,7 +27,10 @@ namespace bstr {
 #endif
 constexpr int FT_MAXTHREADS = BSTR_MAXTHREADS;   // launch bound; the host picks 64..FT_MAXTHREADS per batch
 constexpr int FT_MAXCPT = 16;                  // 16-byte chunks per thread in the index phase
-constexpr int FT_OVL = 4096;                   // look-ahead past the tile end
+#ifndef BSTR_OVL
+#define BSTR_OVL 4096
+#endif
+constexpr int FT_OVL = BSTR_OVL;               // look-ahead past the tile end
 constexpr int FT_MAXREGION = 65504;            // line positions are 16-bit
 constexpr int FT_MINTILE = 8192;
 constexpr int FT_DEFTILE = 40960;
@@ -307,8 +310,18 @@ __device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileG
     return cnt;
 }
 
+// CTA size limit per instantiation: batches of long reads have few records per tile, so the wide
+// windows run with at most FT_WIDETHREADS threads and may keep 168 registers (the 8-word matcher
+// spilled 344 bytes under the 128-register cap of 256-thread CTAs and ran 1.5x slower for it)
+constexpr int FT_WIDETHREADS = 192;
+#ifndef BSTR_WIDE_FROM
+#define BSTR_WIDE_FROM 6
+#endif
+constexpr int FT_WIDEFROM = BSTR_WIDE_FROM;    // narrowest window that gets the smaller CTA limit
+template <int WMAX> constexpr int ft_max_threads() { return WMAX >= FT_WIDEFROM ? FT_WIDETHREADS : FT_MAXTHREADS; }
+
 template <int WMAX>
-__global__ void __launch_bounds__(FT_MAXTHREADS, BSTR_MINCTAS)
+__global__ void __launch_bounds__(ft_max_threads<WMAX>(), BSTR_MINCTAS)
 k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams prm, int illumina,
              BatchState *st, unsigned long long *lb_lines, unsigned long long *lb_out,
              unsigned long long *ticket, uint32_t ntiles, ReadResult *res, uint8_t *out,

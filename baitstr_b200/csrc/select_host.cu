@@ -130,6 +130,7 @@ cudaError_t set_tile_attrs()
 {
     cudaError_t e = cudaFuncSetAttribute(k_fused_tile<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_tile<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_tile<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_tile<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_MAXSMEM);
     return e;
 }
@@ -153,7 +154,13 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threa
     const uint32_t min_thr = ((chunks + FT_MAXCPT - 1) / FT_MAXCPT + 31) & ~31u;
     if (threads < min_thr) threads = min_thr;
     if (threads < 64) threads = 64;
-    if (threads > max_threads) threads = max_threads & ~31u;
+    if (threads > max_threads) {
+        threads = max_threads & ~31u;
+        // fewer record threads than the tile has records: shrink the tile rather than run a
+        // second, nearly empty pass of the per-record phases
+        const double cap = (threads - 32) * rec_bytes / 1.03;
+        if (!ctx->geom_tile && tile > cap && cap >= FT_MINTILE) tile = (uint32_t)cap & ~15u;
+    }
     // a tile may own at most 2 x (threads - 32) records: shrink it for very short records
     const double fit = 1.8 * (threads - 32) * rec_bytes;
     if (tile > fit && !ctx->geom_tile) { tile = (uint32_t)fit & ~15u; if (tile < FT_MINTILE) tile = FT_MINTILE; }
@@ -189,11 +196,11 @@ static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final
     const ScanParams prm = scan_params(ctx);
     // widest bit-parallel window the batch is expected to need (longer reads stay exact through
     // the byte path): L = (record - header - 6) / 2, window = L - 2 (f - 6) for the default
-    // algorithm; 10 % margin for reads longer than the average
+    // algorithm; 4 % margin for reads longer than the average
     const int fe = prm.altalgo && prm.f > 6 ? prm.f - 6 : 0;
-    const double win = (s.rec_bytes - s.hdr_bytes - 6.0) * 0.5 * 1.10 - 2.0 * fe;
-    const int wmax = ctx->force_wmax ? ctx->force_wmax : (win <= 64 ? 2 : (win <= 128 ? 4 : 8));
-    const uint32_t max_threads = FT_MAXTHREADS;
+    const double win = (s.rec_bytes - s.hdr_bytes - 6.0) * 0.5 * 1.04 - 2.0 * fe;
+    const int wmax = ctx->force_wmax ? ctx->force_wmax : (win <= 64 ? 2 : (win <= 128 ? 4 : (win <= 192 ? 6 : 8)));
+    const uint32_t max_threads = wmax >= FT_WIDEFROM ? FT_WIDETHREADS : FT_MAXTHREADS;   // launch bound of k_fused_tile<wmax>
     const TileGeom g = pick_geometry(ctx, s.rec_bytes, max_threads);
     const uint32_t n_tiles = (uint32_t)((nbytes + g.tile - 1) / g.tile);
     unsigned long long *lb_lines = s.d_lb, *lb_out = s.d_lb + n_tiles, *ticket = s.d_lb + 2 * (size_t)n_tiles;
@@ -209,6 +216,7 @@ static int launch_fused(bstr_ctx *ctx, DeviceSlot &s, uint64_t nbytes, int final
     if (n_tiles) {
         if (wmax <= 2) BSTR_LAUNCH_TILE(2);
         else if (wmax <= 4) BSTR_LAUNCH_TILE(4);
+        else if (wmax <= 6) BSTR_LAUNCH_TILE(6);
         else BSTR_LAUNCH_TILE(8);
     }
 #undef BSTR_LAUNCH_TILE
@@ -317,6 +325,9 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
         ctx->exp_mask = ex ? atoi(ex) : 0;
         const char *ge = getenv("BSTR_GEOM");          // tile,threads[,stage] (0 = automatic)
         if (ge) sscanf(ge, "%u,%u,%u", &ctx->geom_tile, &ctx->geom_threads, &ctx->geom_stage);
+        const char *wm = getenv("BSTR_WMAX");          // window-width instantiation: 2, 4, 6 or 8 (0 = automatic)
+        const int w = wm ? atoi(wm) : 0;
+        ctx->force_wmax = (w == 2 || w == 4 || w == 6 || w == 8) ? w : 0;
     }
     e = set_tile_attrs();
     if (e != cudaSuccess) {

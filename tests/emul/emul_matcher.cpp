@@ -42,7 +42,8 @@ struct emul_params { int n, f, kmask, rmhm, altalgo; };
 
 // results: 4 x uint32 per read {fstart, rstart, fck, rck}; same convention as k_match_reads
 // (forward hit reported even when the reverse strand has none).
-// force_w: 0 = dispatch like the device (window_words), else force the width 2/4/8 or 9 (bytes path)
+// force_w: 0 = dispatch like the device (window_words), else force the width 2/4/6/8 or 9 (bytes path);
+// 6 goes through the WMAX = 6 instantiation (the 6-word window exists only there)
 void emul_match_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, const emul_params *ep,
                       int force_w, uint32_t *res)
 {
@@ -58,7 +59,8 @@ void emul_match_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, cons
         bstr::Hit f, rc;
         int w = bstr::window_words(L, prm);
         if (force_w && force_w >= w) w = force_w;
-        bstr::match_read(s, L, prm, w, f, rc);
+        if (force_w == 6) bstr::match_read<6>(s, L, prm, w, f, rc);
+        else bstr::match_read(s, L, prm, w, f, rc);
         const bool sel = f.k && rc.k;
         res[4 * r + 0] = f.k ? (uint32_t)f.start : 0;
         res[4 * r + 1] = sel ? (uint32_t)rc.start : 0;

@@ -269,6 +269,20 @@ def test_full_size_properties(capi):
             assert lines[4 * j + 1][fs:fs + len(hdr[1])] == hdr[1] and fe - fs == len(hdr[1]) * int(hdr[2])
 
 
+@pytest.mark.parametrize("wmax", [2, 4, 6, 8])
+def test_window_width_instantiations(capi, monkeypatch, wmax):
+    """Every k_fused_tile<WMAX> build on reads both narrower and wider than its window: the
+    wider ones must take the exact byte path of the same kernel (no fallback batch)."""
+    monkeypatch.setenv("BSTR_WMAX", str(wmax))
+    for kw in (dict(), dict(ks=[2, 3], f=41), dict(n=3, rmhm=True), dict(altalgo=False, f=10)):
+        with capi.Context(**kw) as ctx:
+            for L, vary in [(100, False), (250, False), (260, True), (150, True)]:
+                raw = util.synth_fastq(4000, L, seed=wmax * 10 + L, p_str=0.6, p_n=0.05, p_lower=0.05,
+                                       vary_len=vary, p_dot=0.01)
+                assert ctx.scan_batch(raw)[0] == oracle.select_buffer(raw, **kw), (wmax, kw, L)
+            assert ctx.stats()["fallback_batches"] == 0
+
+
 def test_generic_kernels_forced(capi, monkeypatch):
     """The staged generic kernels (the fused kernel's fallback) stay byte-exact on their own."""
     monkeypatch.setenv("BSTR_FORCE_GENERIC", "1")

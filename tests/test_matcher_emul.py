@@ -51,7 +51,7 @@ def test_known_answers():
     for seq, kw, fwd, rc in util.KNOWN:
         args = dict(n=kw.get("n", 2), f=kw.get("f", 0), ks=kw.get("ks"),
                     rmhm=kw.get("rmhm", False), altalgo=kw.get("altalgo", True))
-        for w in (0, 2, 4, 8, 9):
+        for w in (0, 2, 4, 6, 8, 9):
             check([seq], force_w=w, **args)
 
 
@@ -70,8 +70,11 @@ def test_fuzz_vs_oracle(seed):
                             200, 250, 255, 256, 257, 300, 400])
             seqs.append(rand_read(rng, L, alpha))
         check(seqs, n=n, f=f, ks=ks, rmhm=rmhm, altalgo=alt)
+        # the 6-word window (129..192 window bases) through the WMAX = 6 instantiation
+        check([s for s in seqs if len(s) <= 192 + 2 * max(0, (f if alt else 0) - 6)][:40], force_w=6,
+              n=n, f=f, ks=ks, rmhm=rmhm, altalgo=alt)
         if it % 4 == 0:
-            check([s for s in seqs if len(s) <= 64 + 2 * max(0, f - 6)][:20], force_w=rng.choice([4, 8, 9]),
+            check([s for s in seqs if len(s) <= 64 + 2 * max(0, f - 6)][:20], force_w=rng.choice([4, 6, 8, 9]),
                   n=n, f=f, ks=ks, rmhm=rmhm, altalgo=alt)
 
 

@@ -6,12 +6,12 @@ import csv, sys
 from collections import defaultdict
 csv.field_size_limit(1 << 30)
 RANGES = {
- 'matcher.cuh': [(44,131,'match: bit helpers'),(143,243,'match: encode planes'),(260,357,'match: scan_period'),
-                 (359,413,'match: pick winner'),(415,486,'match: match_read_bits'),(488,590,'match: long/dispatch'),(592,640,'validate bases')],
+ 'matcher.cuh': [(44,131,'match: bit helpers'),(143,245,'match: encode planes'),(262,373,'match: scan_period'),
+                 (374,428,'match: pick winner'),(429,500,'match: match_read_bits'),(501,611,'match: long/dispatch'),(612,660,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
- 'fused.cuh': [(76,98,'tma/mbarrier'),(100,140,'lookback'),(142,150,'index: nl_mask'),(152,174,'block scan'),(185,195,'record lines'),(197,268,'format: copy'),
-               (270,303,'B index chunks'),(305,345,'A stage'),(346,372,'B index fill'),(373,438,'C record phase + bookkeeping'),(439,487,'D per-record glue'),
-               (488,505,'E offsets'),(506,536,'F format glue + lookback2'),(537,563,'G flush')],
+ 'fused.cuh': [(85,107,'tma/mbarrier'),(109,149,'lookback'),(151,159,'index: nl_mask'),(161,183,'block scan'),(194,203,'record lines'),(204,277,'format: copy'),
+               (279,312,'B index chunks'),(319,360,'A stage'),(361,387,'B index fill'),(388,453,'C record phase + bookkeeping'),(454,502,'D per-record glue'),
+               (503,520,'E offsets'),(521,551,'F format glue + lookback2'),(552,580,'G flush')],
 }
 PRIO = ['matcher.cuh', 'kernels_v1.cuh', 'fused.cuh']
 fname = cols = cur = None; seen = []; stack = defaultdict(dict); inst = {}; samp = {}; thr = {}; stalls = defaultdict(lambda: defaultdict(float))
