@@ -154,13 +154,7 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threa
     const uint32_t min_thr = ((chunks + FT_MAXCPT - 1) / FT_MAXCPT + 31) & ~31u;
     if (threads < min_thr) threads = min_thr;
     if (threads < 64) threads = 64;
-    if (threads > max_threads) {
-        threads = max_threads & ~31u;
-        // fewer record threads than the tile has records: shrink the tile rather than run a
-        // second, nearly empty pass of the per-record phases
-        const double cap = (threads - 32) * rec_bytes / 1.03;
-        if (!ctx->geom_tile && tile > cap && cap >= FT_MINTILE) tile = (uint32_t)cap & ~15u;
-    }
+    if (threads > max_threads) threads = max_threads & ~31u;
     // a tile may own at most 2 x (threads - 32) records: shrink it for very short records
     const double fit = 1.8 * (threads - 32) * rec_bytes;
     if (tile > fit && !ctx->geom_tile) { tile = (uint32_t)fit & ~15u; if (tile < FT_MINTILE) tile = FT_MINTILE; }

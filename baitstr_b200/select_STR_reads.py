@@ -6,13 +6,14 @@ driver script calls), ``MatchPatternsAndReportBest`` (:106), ``ProcessSequence``
 ``ReverseComplement`` (:187), ``PrintSequence`` (:171) and the record type ``fastqsequence``
 (src/fastq.pyx:15-19).  The matching happens in libbaitstr_select.so on the GPU; there is no CPU
 path here.  ``num_processes`` and ``chunksize`` are accepted and never change the output (they
-only size host staging); ``debug_flag`` / ``check_strs`` are accepted, their stderr reports are
-not reproduced.
+only size host staging).  ``check_strs`` (``-c FILE``) prints the reference's stderr report
+(check_strs.py); ``debug_flag`` is accepted, its per-candidate stderr lines are not reproduced.
 """
 import re
 import sys
 
 from . import capi
+from . import check_strs as check_strs_mod
 
 _PATTERN = re.compile(r"^\(\?=\(\(\?=\(\.\{(\d+)\}\)\)\\2\{(\d+),\}\)\)$")      # pyx:350
 _COMPLEMENT = bytes.maketrans(b"atcgnATCGN", b"tagcnTAGCN")                      # pyx:188
@@ -29,13 +30,45 @@ def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_
                      check_strs, only_k_mers, remove_homopolymers, debug_flag, altalgo,
                      num_processes, chunksize):
     sys.stdout.flush()
+    to_check = check_strs_mod.read_str_list(check_strs)                  # pyx:354, before any read
     ctx = capi.Context(n=num_minimum_copies, f=flanking_distance, ks=only_k_mers,
                        rmhm=remove_homopolymers, altalgo=altalgo, illumina=illumina_quals,
                        host_threads=num_processes)
     try:
-        ctx.run_files(list(filenames), out_fd=1, err_fd=2)
+        if not check_strs:
+            ctx.run_files(list(filenames), out_fd=1, err_fd=2)
+        else:
+            _run_files_checked(ctx, list(filenames), to_check)
     finally:
         ctx.close()
+    if check_strs:
+        sys.stderr.flush()
+        check_strs_mod.print_performance_log(to_check)                   # pyx:372-373
+        sys.stderr.flush()
+
+
+def _run_files_checked(ctx, filenames, to_check):
+    """``-c``: the GPU pipeline writes each file's annotated FASTQ to a temporary file, which is
+    copied to stdout unchanged and read by the RegisterSTR report (check_strs.py).  stderr order
+    is the reference's with one worker: the file's "No match" lines, then "Done processing"."""
+    import os
+    import tempfile
+    for fn in filenames:
+        with tempfile.TemporaryFile() as out, tempfile.TemporaryFile() as err:
+            failure = None
+            try:
+                ctx.run_files([fn], out_fd=out.fileno(), err_fd=err.fileno())
+            except Exception as e:                                      # noqa: BLE001 -- re-raised below
+                failure = e
+            out.seek(0)
+            data = out.read()
+            os.write(1, data)                 # everything before a bad record is still printed
+            check_strs_mod.register_annotated_fastq(data, to_check)
+            sys.stderr.flush()
+            err.seek(0)
+            os.write(2, err.read())           # "Done processing <file>" (pyx:370)
+            if failure is not None:
+                raise failure
 
 
 def _periods_and_copies(patterns):

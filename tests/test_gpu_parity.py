@@ -236,6 +236,30 @@ def test_cli_end_to_end(capi, tmp_path):
     assert r.returncode == 1 and b"bad.fq" in r.stderr
 
 
+def test_cli_check_strs(capi, tmp_path):
+    """`-c LIST` end to end through the drop-in CLI: stdout unchanged, stderr equal to the live
+    reference's (tests/golden/check_strs.json: "No match" lines, "Done processing", the
+    reference's "Found 0 reads" log)."""
+    import json
+    cases = json.load(open(os.path.join(util.ROOT, "tests", "golden", "check_strs.json")))
+    paths = []
+    for i in (1, 2):
+        p = str(tmp_path / ("testdata_%d.fq" % i))
+        open(p, "wb").write(util.gz_read("testdata_%d.fq.gz" % i))
+        paths.append(p)
+    cli = os.path.join(util.ROOT, "bin", "select_STR_reads")
+    for case in cases:
+        chk = str(tmp_path / "check.txt")
+        open(chk, "w").write(case["check_file"])
+        plain = subprocess.run([sys.executable, cli] + case["flags"] + paths, capture_output=True)
+        r = subprocess.run([sys.executable, cli] + case["flags"] + ["-c", chk] + paths, capture_output=True)
+        assert r.returncode == 0, r.stderr
+        assert r.stdout == plain.stdout
+        assert r.stdout == b"".join(oracle.select_buffer(open(p, "rb").read(), **util.flags_to_kwargs(case["flags"]))
+                                    for p in paths)
+        assert r.stderr.decode().replace(str(tmp_path) + "/", "") == case["stderr"]
+
+
 def test_full_size_properties(capi):
     """BASELINE-sized batches (1M x 100 bp, 0.5M x 150 bp): every selected record is the
     input record with an annotated header (round trip), order is preserved, counts agree
