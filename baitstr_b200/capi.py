@@ -50,7 +50,8 @@ class BenchOut(C.Structure):
 EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "bstr_scan_batch",
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
-           "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip"]
+           "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
+           "bstr_debug_codes_cap"]
 
 _lib = None
 
@@ -89,6 +90,11 @@ def load_library():
     lib.bstr_collect_batch.restype = C.c_int
     lib.bstr_match_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.bstr_match_reads.restype = C.c_int
+    lib.bstr_debug_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]
+    lib.bstr_debug_reads.restype = C.c_int
+    lib.bstr_debug_codes_cap.argtypes = [C.c_void_p, C.c_uint32]
+    lib.bstr_debug_codes_cap.restype = C.c_uint32
     lib.bstr_bench_resident.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
                                         C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(BenchOut)]
     lib.bstr_bench_resident.restype = C.c_int
@@ -278,6 +284,30 @@ class Context:
         if rc:
             self._raise(rc)
         return res
+
+    def debug_reads(self, seqs):
+        """list of bytes -> per read (info[8], forward codes, reverse-strand codes): the -d report
+        of include/baitstr_select.h: bstr_debug_reads."""
+        nreads = len(seqs)
+        off = np.zeros(nreads + 1, dtype=np.uint64)
+        coff = np.zeros(nreads + 1, dtype=np.uint64)
+        if nreads:
+            off[1:] = np.cumsum([len(s) for s in seqs])
+            caps = [2 * self._lib.bstr_debug_codes_cap(self._ctx, len(s)) for s in seqs]
+            coff[1:] = np.cumsum(caps)
+        blob = np.frombuffer(b"".join(seqs) + b"\0", dtype=np.uint8)
+        codes = np.zeros(int(coff[-1]) + 1, dtype=np.uint8)
+        info = np.zeros((nreads, 8), dtype=np.uint32)
+        rc = self._lib.bstr_debug_reads(self._ctx, blob.ctypes.data, off.ctypes.data, nreads,
+                                        coff.ctypes.data, codes.ctypes.data, info.ctypes.data)
+        if rc:
+            self._raise(rc)
+        out = []
+        for i in range(nreads):
+            lo, hi = int(coff[i]), int(coff[i + 1])
+            half = (hi - lo) // 2
+            out.append((info[i], codes[lo:lo + int(info[i, 0])], codes[lo + half:lo + half + int(info[i, 4])]))
+        return out
 
     def run_files(self, paths, out_fd=1, err_fd=2):
         arr = (C.c_char_p * len(paths))(*[os.fsencode(p) for p in paths])

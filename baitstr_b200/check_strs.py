@@ -97,16 +97,27 @@ def register_str(string, match, rc_match, to_check, err=None):
     return False
 
 
-def register_annotated_fastq(data, to_check, err=None):
-    """Run register_str over every record of an annotated FASTQ buffer (bytes) as written by the
-    select stage: ``@name\\tfmotif\\tfcopies\\tfstart\\tfend\\trmotif\\trcopies\\trstart\\trend``."""
+def annotated_fastq_lines(data, to_check):
+    """register_str over every record of an annotated FASTQ buffer (bytes) as written by the
+    select stage (``@name\\tfmotif\\tfcopies\\tfstart\\tfend\\trmotif\\trcopies\\trstart\\trend``):
+    yields, per record, the "No match" line or "" when a listed STR was found."""
+    import io
     lines = data.split(b"\n")
     for i in range(0, len(lines) - 3, 4):
         fields = lines[i].decode("latin-1").rsplit("\t", 8)       # the name itself may hold tabs
         seq = lines[i + 1].decode("latin-1")
         match = (fields[1], int(fields[2]), int(fields[3]), int(fields[4]))
         rc_match = (fields[5], int(fields[6]), int(fields[7]), int(fields[8]))
-        register_str(seq, match, rc_match, to_check, err)
+        buf = io.StringIO()
+        register_str(seq, match, rc_match, to_check, buf)
+        yield buf.getvalue()
+
+
+def register_annotated_fastq(data, to_check, err=None):
+    """All "No match" lines of an annotated FASTQ buffer, written to `err`."""
+    err = sys.stderr if err is None else err
+    for line in annotated_fastq_lines(data, to_check):
+        err.write(line)
 
 
 def print_performance_log(to_check, err=None):

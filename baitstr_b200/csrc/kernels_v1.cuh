@@ -378,6 +378,26 @@ k_match_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, ScanParams p
     res[r] = out;
 }
 
+// -d/--debug report of ProcessSequence (select_STR_reads.pyx:294-311) for one read per thread:
+// the rejection codes of the forward strand, and -- only if the forward strand has a best
+// match, as in the reference -- those of the reverse complement.  codes of read r live at
+// [coff[r], coff[r+1]): forward strand first, reverse strand from the middle of the slot.
+// info[8 r ..] = {fwd count, fwd is None, fwd tail code, fwd tail value, same four for rc};
+// tail = the -x algorithm's message about its winner ("Insufficient 5'/3' flank.: <value>").
+__global__ void __launch_bounds__(128)
+k_debug_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, ScanParams prm, const uint64_t *coff,
+              uint8_t *codes, uint32_t *info)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const uint8_t *seq = seqs + off[r];
+    const int L = (int)(off[r + 1] - off[r]);
+    const uint64_t half = (coff[r + 1] - coff[r]) / 2;
+    uint32_t o[8];
+    debug_read(seq, L, prm, codes + coff[r], codes + coff[r] + half, o);
+    for (int i = 0; i < 8; i++) info[8 * r + i] = o[i];
+}
+
 __global__ void k_flush_l2(uint32_t *buf, uint64_t nwords, uint32_t v)
 {
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords;

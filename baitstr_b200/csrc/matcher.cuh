@@ -514,7 +514,8 @@ __device__ __forceinline__ uint8_t strand_char(const uint8_t *seq, int L, bool r
     return c;
 }
 
-__device__ inline Hit match_strand_bytes(const uint8_t *seq, int L, bool rc, const ScanParams &prm)
+__device__ inline Hit match_strand_bytes(const uint8_t *seq, int L, bool rc, const ScanParams &prm,
+                                         Hit *pre = nullptr /* -x: the winner before its flank / -r tests */)
 {
     const int n = prm.n < 1 ? 1 : prm.n;
     int b_len = 0, b_c = 0, b_s = 0, b_k = 0;
@@ -559,6 +560,7 @@ __device__ inline Hit match_strand_bytes(const uint8_t *seq, int L, bool rc, con
         }
     }
     Hit h; h.k = 0; h.copies = 0; h.start = 0;
+    if (pre) { pre->k = b_k; pre->copies = b_c; pre->start = b_s; }
     if (b_k == 0) return h;
     if (!prm.altalgo) {
         if (b_s < prm.f || L - (b_s + b_len) < prm.f) return h;
@@ -580,6 +582,78 @@ __device__ inline void match_read_bytes(const uint8_t *seq, int L, const ScanPar
     fwd = match_strand_bytes(seq, L, false, prm);
     if (fwd.k == 0) return;
     rc = match_strand_bytes(seq, L, true, prm);
+}
+
+// ---------------------------------------------------------------------------------------
+// -d/--debug (select_STR_reads.pyx:76-87, 138-140): one code per regex hit the reference
+// rejects with a message, in the reference's order (patterns by ascending period, starts
+// ascending): 'N' = "N in motif.", '5' = "Insufficient 5' flank.", '3' = "Insufficient 3'
+// flank." (the last two only in the default algorithm; homopolymer hits under -r are dropped
+// silently, pyx:89).  Returns the number of codes; out may be null (count only).
+// ---------------------------------------------------------------------------------------
+__device__ inline uint32_t debug_strand_codes(const uint8_t *seq, int L, bool rc, const ScanParams &prm,
+                                              uint8_t *out)
+{
+    const int n = prm.n < 1 ? 1 : prm.n;
+    uint32_t cnt = 0;
+    for (int k = 2; k <= 6; k++) {
+        if (!(prm.kmask & (1 << k)) || L < k * n) continue;
+        int reach = -1;                      // first p >= i with t[p] != t[p+k] (or p = L-k): run(i) = reach - i
+        for (int i = 0; i + k * n <= L; i++) {
+            if (reach < i) {
+                reach = i;
+                while (reach + k < L && strand_char(seq, L, rc, reach) == strand_char(seq, L, rc, reach + k)) reach++;
+            }
+            const int c = 1 + (reach - i) / k;
+            if (c < n) continue;
+            bool has_n = false;
+            for (int j = 0; j < k; j++) has_n |= strand_char(seq, L, rc, i + j) == 'N';
+            uint8_t code = 0;
+            if (has_n) code = 'N';
+            else if (prm.altalgo) {
+                if (i < prm.f) code = '5';
+                else if (L - (i + k * c) < prm.f) code = '3';
+            }
+            if (code) {
+                if (out) out[cnt] = code;
+                cnt++;
+            }
+        }
+    }
+    return cnt;
+}
+
+// The -d report of one read (ProcessSequence, pyx:294-311): o[0..3] = forward strand {number of
+// codes, 1 if the strand has no best match, tail code, tail value}, o[4..7] the same for the
+// reverse complement, which the reference only scans when the forward strand has a match.
+// tail = the -x algorithm's message about its winner (pyx:157-163).
+__device__ inline void debug_read(const uint8_t *seq, int L, const ScanParams &prm, uint8_t *codes_fwd,
+                                  uint8_t *codes_rc, uint32_t (&o)[8])
+{
+    o[0] = 0; o[1] = 1; o[2] = 0; o[3] = 0; o[4] = 0; o[5] = 1; o[6] = 0; o[7] = 0;
+    for (int strand = 0; strand < 2; strand++) {
+        const bool rc = strand == 1;
+        o[4 * strand] = debug_strand_codes(seq, L, rc, prm, rc ? codes_rc : codes_fwd);
+        Hit pre;
+        const Hit h = match_strand_bytes(seq, L, rc, prm, &pre);
+        o[4 * strand + 1] = h.k == 0;
+        if (!prm.altalgo && pre.k) {
+            const int end = pre.start + pre.k * pre.copies;
+            if (pre.start < prm.f) { o[4 * strand + 2] = '5'; o[4 * strand + 3] = (uint32_t)pre.start; }
+            else if (L - end < prm.f) { o[4 * strand + 2] = '3'; o[4 * strand + 3] = (uint32_t)(L - end); }
+        }
+        if (h.k == 0) break;                               // pyx:303-305: no second strand
+    }
+}
+
+// upper bound of debug_strand_codes for a read of length L (every start of every period)
+__host__ __device__ inline uint32_t debug_codes_cap(int L, int n, int kmask)
+{
+    if (n < 1) n = 1;
+    uint32_t cap = 0;
+    for (int k = 2; k <= 6; k++)
+        if ((kmask & (1 << k)) && L >= k * n) cap += (uint32_t)(L - k * n + 1);
+    return cap;
 }
 
 // number of 32-bit words the bit-parallel window of a read of length L needs (0: no window)

@@ -7,13 +7,15 @@ driver script calls), ``MatchPatternsAndReportBest`` (:106), ``ProcessSequence``
 (src/fastq.pyx:15-19).  The matching happens in libbaitstr_select.so on the GPU; there is no CPU
 path here.  ``num_processes`` and ``chunksize`` are accepted and never change the output (they
 only size host staging).  ``check_strs`` (``-c FILE``) prints the reference's stderr report
-(check_strs.py); ``debug_flag`` is accepted, its per-candidate stderr lines are not reproduced.
+(check_strs.py), ``debug_flag`` (``-d``) the per-read blocks of ProcessSequence (debug_report.py,
+enumerated on the GPU by bstr_debug_reads).
 """
 import re
 import sys
 
 from . import capi
 from . import check_strs as check_strs_mod
+from . import debug_report
 
 _PATTERN = re.compile(r"^\(\?=\(\(\?=\(\.\{(\d+)\}\)\)\\2\{(\d+),\}\)\)$")      # pyx:350
 _COMPLEMENT = bytes.maketrans(b"atcgnATCGN", b"tagcnTAGCN")                      # pyx:188
@@ -35,10 +37,10 @@ def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_
                        rmhm=remove_homopolymers, altalgo=altalgo, illumina=illumina_quals,
                        host_threads=num_processes)
     try:
-        if not check_strs:
+        if not check_strs and not debug_flag:
             ctx.run_files(list(filenames), out_fd=1, err_fd=2)
         else:
-            _run_files_checked(ctx, list(filenames), to_check)
+            _run_files_reported(ctx, list(filenames), to_check if check_strs else None, debug_flag)
     finally:
         ctx.close()
     if check_strs:
@@ -47,10 +49,11 @@ def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_
         sys.stderr.flush()
 
 
-def _run_files_checked(ctx, filenames, to_check):
-    """``-c``: the GPU pipeline writes each file's annotated FASTQ to a temporary file, which is
-    copied to stdout unchanged and read by the RegisterSTR report (check_strs.py).  stderr order
-    is the reference's with one worker: the file's "No match" lines, then "Done processing"."""
+def _run_files_reported(ctx, filenames, to_check, debug_flag):
+    """``-c`` and/or ``-d``: the GPU pipeline writes each file's annotated FASTQ to a temporary
+    file, which is copied to stdout unchanged; then the file's stderr reports follow in the
+    reference's order with one worker: per read its -d block (debug_report.py) and, if it was
+    selected, its -c "No match" line (check_strs.py); then "Done processing" (pyx:370)."""
     import os
     import tempfile
     for fn in filenames:
@@ -63,10 +66,20 @@ def _run_files_checked(ctx, filenames, to_check):
             out.seek(0)
             data = out.read()
             os.write(1, data)                 # everything before a bad record is still printed
-            check_strs_mod.register_annotated_fastq(data, to_check)
+            check_lines = iter(check_strs_mod.annotated_fastq_lines(data, to_check)) if to_check is not None else None
+            if debug_flag and failure is None:
+                # a selected read's "No match" line follows its own block (both come out of the
+                # same ProcessSequence call, pyx:296-317)
+                for block, selected in debug_report.file_blocks(ctx, fn):
+                    sys.stderr.write(block)
+                    if selected and check_lines is not None:
+                        sys.stderr.write(next(check_lines, ""))
+            if check_lines is not None:
+                for line in check_lines:
+                    sys.stderr.write(line)
             sys.stderr.flush()
             err.seek(0)
-            os.write(2, err.read())           # "Done processing <file>" (pyx:370)
+            os.write(2, err.read())
             if failure is not None:
                 raise failure
 

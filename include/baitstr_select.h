@@ -135,6 +135,21 @@ int bstr_collect_batch(bstr_ctx *ctx, int lane, bstr_batch_out *out);
 int bstr_match_reads(bstr_ctx *ctx, const uint8_t *seqs, const uint64_t *offsets,
                      uint64_t nreads, bstr_read_result *results);
 
+/* -d/--debug: what the reference prints per read when debug_flag is set
+ * (select_STR_reads.pyx:296-311 with :76-87 / :138-140 and :157-163).  For read i the codes of
+ * the regex hits the reference rejects with a message -- 'N' "N in motif.", '5' "Insufficient
+ * 5' flank.", '3' "Insufficient 3' flank.", in the reference's order -- are written to
+ * codes[code_offsets[i] ...) for the forward strand and to the second half of the slot for the
+ * reverse complement; every slot must hold 2 * bstr_debug_codes_cap(ctx, read length) bytes.
+ * info[8 i ..] = {forward: number of codes, 1 if the strand has no best match ("0 valid
+ * matches."), tail code and value of the -x algorithm's message about its winner ('5' / '3',
+ * "Insufficient 5' flank.: <value>"), then the same four for the reverse strand, which the
+ * reference only looks at when the forward strand has a match}.  Sequences as for
+ * bstr_match_reads. */
+int bstr_debug_reads(bstr_ctx *ctx, const uint8_t *seqs, const uint64_t *offsets, uint64_t nreads,
+                     const uint64_t *code_offsets, uint8_t *codes, uint32_t *info);
+uint32_t bstr_debug_codes_cap(const bstr_ctx *ctx, uint32_t read_length);
+
 /* Upload `nbatches` batches (each a whole number of records, as bstr_scan_batch with
  * final = 1) and run the device pipeline over all of them `warmup + steps` times with the
  * input resident in HBM (no host copies inside the timed region); optionally evict L2

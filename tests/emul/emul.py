@@ -55,6 +55,23 @@ def match_reads(seqs, n=2, f=31, ks=None, rmhm=False, altalgo=True, force_w=0):
     return res
 
 
+def debug_read(seq, n=2, f=31, ks=None, rmhm=False, altalgo=True):
+    """bytes -> (info[8], forward codes, reverse-strand codes) through matcher.cuh: debug_read."""
+    km = 0
+    for k in (ks or [2, 3, 4, 5, 6]):
+        km |= 1 << k
+    L = lib()
+    L.emul_debug_codes_cap.restype = C.c_uint32
+    cap = L.emul_debug_codes_cap(len(seq), n, km)
+    fwd = np.zeros(cap + 1, dtype=np.uint8)
+    rc = np.zeros(cap + 1, dtype=np.uint8)
+    info = np.zeros(8, dtype=np.uint32)
+    p = Params(n, f, km, int(rmhm), int(altalgo))
+    L.emul_debug_read(bytes(seq), len(seq), C.byref(p), fwd.ctypes.data_as(C.c_void_p),
+                      rc.ctypes.data_as(C.c_void_p), info.ctypes.data_as(C.c_void_p))
+    return info, fwd[:int(info[0])], rc[:int(info[4])]
+
+
 def bases_invalid(data, misalign=0):
     buf = C.create_string_buffer(b"\0" * misalign + bytes(data))
     return bool(lib().emul_bases_invalid(C.cast(C.addressof(buf) + misalign, C.c_char_p), len(data)))

@@ -70,6 +70,23 @@ void emul_match_reads(const uint8_t *seqs, const uint64_t *off, uint64_t n, cons
     }
 }
 
+// -d report of one read through the device code (matcher.cuh: debug_read); codes_fwd / codes_rc
+// need bstr::debug_codes_cap bytes each
+void emul_debug_read(const uint8_t *seq, int L, const emul_params *ep, uint8_t *codes_fwd, uint8_t *codes_rc,
+                     uint32_t *info)
+{
+    bstr::ScanParams prm;
+    prm.n = ep->n < 1 ? 1 : ep->n; prm.f = ep->f < 0 ? 0 : ep->f; prm.kmask = ep->kmask;
+    prm.rmhm = ep->rmhm; prm.altalgo = ep->altalgo;
+    uint8_t *buf = (uint8_t *)calloc((size_t)L + 192, 1);
+    memcpy(buf + 64, seq, (size_t)L);
+    uint32_t o[8];
+    bstr::debug_read(buf + 64, L, prm, codes_fwd, codes_rc, o);
+    for (int i = 0; i < 8; i++) info[i] = o[i];
+    free(buf);
+}
+uint32_t emul_debug_codes_cap(int L, int n, int kmask) { return bstr::debug_codes_cap(L, n, kmask); }
+
 // exhaustive check hook for the SWAR base validator: returns 1 if the device code calls the
 // L bytes at p (any alignment) invalid
 int emul_bases_invalid(const uint8_t *p, int L)

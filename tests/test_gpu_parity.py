@@ -260,6 +260,31 @@ def test_cli_check_strs(capi, tmp_path):
         assert r.stderr.decode().replace(str(tmp_path) + "/", "") == case["stderr"]
 
 
+def test_cli_debug_report(capi, tmp_path):
+    """`-d` (and `-d -c LIST`) end to end through the drop-in CLI: stdout unchanged, stderr equal
+    to the live reference's with one worker (tests/golden/debug_report.json.gz); the rejected
+    regex hits are enumerated by k_debug_reads."""
+    import gzip
+    import json
+    gold = json.loads(gzip.open(os.path.join(util.ROOT, "tests", "golden", "debug_report.json.gz")).read())
+    fq = str(tmp_path / "debug.fq")
+    open(fq, "wb").write(gold["fastq"].encode("latin-1"))
+    chk = str(tmp_path / "check.txt")
+    open(chk, "w").write(gold["check_file"])
+    cli = os.path.join(util.ROOT, "bin", "select_STR_reads")
+    for case in gold["cases"]:
+        flags = [chk if f == "CHECKFILE" else f for f in case["flags"]]
+        plain = [f for f in case["flags"] if f not in ("-c", "CHECKFILE")]
+        r = subprocess.run([sys.executable, cli, "-d"] + flags + [fq], capture_output=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        assert r.stdout == oracle.select_buffer(gold["fastq"].encode("latin-1"), **util.flags_to_kwargs(plain))
+        assert r.stderr.decode("latin-1").replace(str(tmp_path) + "/", "") == case["stderr"], case["flags"]
+    # the hook itself: a slot smaller than the worst case is refused, not overrun
+    with capi.Context() as ctx:
+        out = ctx.debug_reads([b"GGCATATATATCG", b"", b"ACGT" * 40])
+        assert len(out) == 3 and int(out[1][0][1]) == 1
+
+
 def test_full_size_properties(capi):
     """BASELINE-sized batches (1M x 100 bp, 0.5M x 150 bp): every selected record is the
     input record with an annotated header (round trip), order is preserved, counts agree
