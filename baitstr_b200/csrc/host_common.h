@@ -57,6 +57,7 @@ struct bstr_ctx {
     int sm_count;
     int exp_mask;                  // BSTR_EXP: phase-skipping bits for profiling experiments
     uint32_t geom_tile, geom_threads, geom_stage;   // BSTR_GEOM overrides (0 = automatic)
+    bool auto_tile_off;            // BSTR_AUTOTILE=0
     int force_wmax;                // BSTR_WMAX: 2, 4, 6 or 8 (0 = from the record size)
     bool force_generic;            // BSTR_FORCE_GENERIC=1: staged kernels only (tests)
     cudaStream_t stream, stream2;  // stream2: second launch stream of bstr_bench_resident

@@ -138,10 +138,35 @@ cudaError_t set_tile_attrs()
 // Tile geometry for a batch whose records average `rec_bytes` bytes (fused.cuh: TileGeom).
 // The tile is sized so that it owns about as many records as the CTA has threads; the
 // CTA size follows from the tile size.  BSTR_GEOM=tile,threads[,stage] overrides (sweeps).
+static TileGeom geometry_for_tile(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threads, uint32_t tile0);
+
 TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threads)
 {
     if (rec_bytes < 16) rec_bytes = 16;
-    uint32_t tile = ctx->geom_tile ? ctx->geom_tile : FT_DEFTILE;
+    if (ctx->geom_tile || ctx->auto_tile_off) return geometry_for_tile(ctx, rec_bytes, max_threads, ctx->geom_tile);
+    // Automatic tile: the largest one (1 KiB steps) that still lets two CTAs share an SM (228 KB
+    // per SM, 1 KB reserved per CTA) -- per-tile latencies (ticket, bulk copy, look-backs) are
+    // amortised over more records.  If the last record warp of such a tile would be less than
+    // half full, the tile is cut back to a whole number of warps instead: a nearly empty warp
+    // costs as many issue slots as a full one (C5: 140 records per tile ran 8 % slower than 127).
+    const uint32_t budget = 228u * 1024u / 2u - 1024u;
+    uint32_t tile = FT_DEFTILE;
+    for (uint32_t t = 49152; t > FT_DEFTILE; t -= 1024) {
+        const TileGeom g = geometry_for_tile(ctx, rec_bytes, max_threads, t);      // may come back smaller than t
+        if (g.smem_bytes <= budget) { if (g.tile > tile) tile = g.tile; break; }
+    }
+    const double recs = tile / rec_bytes;
+    const double warps = floor(recs / 32.0);
+    if (warps >= 1.0 && recs / 32.0 - warps < 0.5) {
+        const uint32_t cut = (uint32_t)(warps * 32.0 * rec_bytes * 0.99) & ~15u;
+        if (cut >= FT_DEFTILE * 3 / 4) tile = cut;
+    }
+    return geometry_for_tile(ctx, rec_bytes, max_threads, tile);
+}
+
+static TileGeom geometry_for_tile(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threads, uint32_t tile0)
+{
+    uint32_t tile = tile0 ? tile0 : FT_DEFTILE;
     if (tile < FT_MINTILE) tile = FT_MINTILE;
     tile &= ~15u;
     if (tile + FT_OVL > FT_MAXREGION) tile = (FT_MAXREGION - FT_OVL) & ~15u;
@@ -155,6 +180,9 @@ TileGeom pick_geometry(const bstr_ctx *ctx, double rec_bytes, uint32_t max_threa
     if (threads < min_thr) threads = min_thr;
     if (threads < 64) threads = 64;
     if (threads > max_threads) threads = max_threads & ~31u;
+    // the index phase gives every thread at most FT_MAXCPT 16-byte chunks of the window
+    const uint32_t max_tile = (threads * FT_MAXCPT * 16u - FT_OVL) & ~15u;
+    if (tile > max_tile) tile = max_tile;
     // a tile may own at most 2 x (threads - 32) records: shrink it for very short records
     const double fit = 1.8 * (threads - 32) * rec_bytes;
     if (tile > fit && !ctx->geom_tile) { tile = (uint32_t)fit & ~15u; if (tile < FT_MINTILE) tile = FT_MINTILE; }
@@ -319,6 +347,8 @@ bstr_ctx *bstr_create(const bstr_params *p, char *err, size_t errlen)
         ctx->exp_mask = ex ? atoi(ex) : 0;
         const char *ge = getenv("BSTR_GEOM");          // tile,threads[,stage] (0 = automatic)
         if (ge) sscanf(ge, "%u,%u,%u", &ctx->geom_tile, &ctx->geom_threads, &ctx->geom_stage);
+        const char *at = getenv("BSTR_AUTOTILE");      // 0: the fixed 40 KiB default tile (A/B measurements)
+        ctx->auto_tile_off = at && at[0] == '0';
         const char *wm = getenv("BSTR_WMAX");          // window-width instantiation: 2, 4, 6 or 8 (0 = automatic)
         const int w = wm ? atoi(wm) : 0;
         ctx->force_wmax = (w == 2 || w == 4 || w == 6 || w == 8) ? w : 0;
