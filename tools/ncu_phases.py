@@ -7,7 +7,7 @@ from collections import defaultdict
 csv.field_size_limit(1 << 30)
 RANGES = {
  'matcher.cuh': [(44,131,'match: bit helpers'),(143,245,'match: encode planes'),(262,373,'match: scan_period'),
-                 (374,428,'match: pick winner'),(429,500,'match: match_read_bits'),(501,611,'match: long/dispatch'),(612,660,'validate bases')],
+                 (374,428,'match: pick winner'),(429,500,'match: match_read_bits'),(501,685,'match: long/dispatch'),(686,722,'validate bases')],
  'kernels_v1.cuh': [(32,37,'index: nl_flags'),(210,228,'outlen'),(288,304,'format: digits/upper/comp')],
  'fused.cuh': [(85,107,'tma/mbarrier'),(109,149,'lookback'),(151,159,'index: nl_mask'),(161,183,'block scan'),(194,203,'record lines'),(204,277,'format: copy'),
                (279,312,'B index chunks'),(319,360,'A stage'),(361,387,'B index fill'),(388,453,'C record phase + bookkeeping'),(454,502,'D per-record glue'),
