@@ -195,6 +195,24 @@ static TileGeom geometry_for_tile(const bstr_ctx *ctx, double rec_bytes, uint32_
     return g;
 }
 
+}  // namespace bstr
+
+// Host-only test hook (no GPU): the tile geometry pick_geometry() chooses for batches whose
+// records average `record_bytes` bytes, for the kernel instantiation with `window_words`
+// (2, 4, 6, 8).  out = {tile, threads, region, chunks, chunks per thread, recmax, stage, smem}.
+extern "C" int bstr_geometry_probe(double record_bytes, int window_words, uint32_t out[8])
+{
+    if (!out || !(record_bytes > 0)) return BSTR_ERR_PARAM;
+    bstr_ctx probe;                                     // zeroed: no overrides, automatic tile
+    const uint32_t max_threads = window_words >= bstr::FT_WIDEFROM ? bstr::FT_WIDETHREADS : bstr::FT_MAXTHREADS;
+    const bstr::TileGeom g = bstr::pick_geometry(&probe, record_bytes, max_threads);
+    out[0] = g.tile; out[1] = g.threads; out[2] = g.region; out[3] = g.chunks; out[4] = g.cpt;
+    out[5] = g.recmax; out[6] = g.stage; out[7] = g.smem_bytes;
+    return BSTR_OK;
+}
+
+namespace bstr {
+
 // first bytes of a host batch -> average record size (4 lines per record); *hdr_bytes gets
 // the length of the first line (header), which separates read length from record size
 double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes, double *hdr_bytes)

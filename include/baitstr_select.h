@@ -165,6 +165,13 @@ void bstr_host_free(void *p);
 void bstr_get_stats(const bstr_ctx *ctx, bstr_stats *st);
 void bstr_reset_stats(bstr_ctx *ctx);
 
+/* Host-only test hook (no GPU needed): the tile geometry of the fused kernel (csrc/fused.cuh:
+ * TileGeom) for batches whose records average record_bytes bytes, for the instantiation with
+ * window_words = 2, 4, 6 or 8.  out = {tile bytes, CTA threads, window bytes, 16-byte chunks,
+ * chunks per thread, record slots, staging bytes, dynamic shared memory}.  No counterpart in
+ * the reference (its chunk size is the -s option, src/select_STR_reads.pyx:321-337). */
+int bstr_geometry_probe(double record_bytes, int window_words, uint32_t out[8]);
+
 /* Host-only test hook for the ingest side (no GPU needed): inflate the gzip file `path`
  * (single- or multi-member, bgzip included) on `threads` threads with the parallel inflater
  * that bstr_run_files uses for "*.gz" inputs (the reference inflates on one thread through

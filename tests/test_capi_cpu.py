@@ -76,3 +76,31 @@ def test_cli_contract_without_gpu():
     assert r.returncode == 3 and "usage:" in r.stderr
     r = _cli("--flank", "5")          # unique-prefix long option, then no files
     assert r.returncode == 3
+
+
+def test_tile_geometry_invariants():
+    """pick_geometry (csrc/select_host.cu) over record sizes and kernel instantiations: what the
+    fused kernel relies on (fused.cuh) must hold for every pick.  No GPU involved."""
+    import ctypes as C
+    from baitstr_b200 import capi
+    lib = capi.load_library()
+    lib.bstr_geometry_probe.argtypes = [C.c_double, C.c_int, C.POINTER(C.c_uint32)]
+    lib.bstr_geometry_probe.restype = C.c_int
+    out = (C.c_uint32 * 8)()
+    picks = {}
+    for w in (2, 4, 6, 8):
+        for rec in [16, 40, 90, 124, 223, 224, 260, 323, 400, 524, 700, 1024, 1500, 2100, 4000, 9000]:
+            assert lib.bstr_geometry_probe(float(rec), w, out) == 0
+            tile, thr, region, chunks, cpt, recmax, stage, smem = list(out)
+            ctx = (w, rec, list(out))
+            assert tile % 16 == 0 and tile >= 8192 and region == tile + 4096 and region <= 65504, ctx
+            assert thr % 32 == 0 and 64 <= thr <= (192 if w >= 6 else 256), ctx
+            assert chunks == region // 16 and cpt * thr >= chunks and cpt <= 16, ctx     # FT_MAXCPT
+            assert recmax == 2 * thr and smem <= 200 * 1024, ctx                           # FT_MAXSMEM
+            if rec >= 90:
+                assert 2 * (smem + 1024) <= 228 * 1024, ctx                                # two CTAs per SM
+                assert stage >= tile * (1 + 48.0 / rec), ctx
+            picks[(w, rec)] = (tile, thr)
+    # the picks the round-1 measurements were taken with (DESIGN.md 4.3)
+    assert picks[(2, 223)] == (41984, 256) and picks[(4, 323)] == (40928, 192) and picks[(6, 524)] == (45056, 192)
+    assert lib.bstr_geometry_probe(0.0, 2, out) != 0
