@@ -1,4 +1,8 @@
 #!/bin/bash
+# needs the A/B build first (not made by the Makefile):
+#   cd baitstr_b200/csrc && nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC \
+#     -DBSTR_MAXTHREADS=224 -DBSTR_MINCTAS=3 -c select_host.cu -o /tmp/occ3.o && nvcc -shared -gencode arch=compute_100a,code=sm_100a \
+#     -o ../libbaitstr_select_occ3.so /tmp/occ3.o stream_host.o pinflate.o -lz -lpthread -cudart shared
 # occupancy experiment: phases A-E only (BSTR_EXP 4|8 = no format, no flush; +16 = dummy stage) at 2 / 3 CTAs per SM
 run() { # label, lib, exp, geom
   BSTR_LIB=$2 BSTR_EXP=$3 BSTR_GEOM=$4 python bench.py --reads 4000000 --steps 3 --warmup 3 --no-cpu --no-ingest 2>/dev/null | python -c "
