@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 def library_path():
@@ -36,7 +36,8 @@ class Stats(C.Structure):
     _fields_ = [("records", C.c_uint64), ("selected", C.c_uint64), ("in_bytes", C.c_uint64),
                 ("out_bytes", C.c_uint64), ("batches", C.c_uint64), ("fallback_batches", C.c_uint64),
                 ("h2d_ms", C.c_double),
-                ("kernel_ms", C.c_double), ("d2h_ms", C.c_double), ("wall_ms", C.c_double)]
+                ("kernel_ms", C.c_double), ("d2h_ms", C.c_double), ("wall_ms", C.c_double),
+                ("device_batches", C.c_uint64 * 16)]
 
 
 class BenchOut(C.Structure):
@@ -51,7 +52,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
-           "bstr_debug_codes_cap", "bstr_geometry_probe"]
+           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe"]
 
 _lib = None
 
@@ -98,6 +99,9 @@ def load_library():
     lib.bstr_bench_resident.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
                                         C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(BenchOut)]
     lib.bstr_bench_resident.restype = C.c_int
+    lib.bstr_pcie_probe.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                    C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.bstr_pcie_probe.restype = C.c_int
     lib.bstr_host_alloc.argtypes = [C.c_size_t]
     lib.bstr_host_alloc.restype = C.c_void_p
     lib.bstr_host_free.argtypes = [C.c_void_p]
@@ -331,10 +335,25 @@ class Context:
                 "n_records": bo.n_records, "n_selected": bo.n_selected, "in_bytes": bo.in_bytes,
                 "out_bytes": bo.out_bytes, "out_checksum": bo.out_checksum}
 
+    def pcie_probe(self, jobs, out_bytes, mode, reps=1):
+        """bstr_pcie_probe: jobs = [(buffer, offset, nbytes)], out_bytes per job; mode 1 = H2D,
+        2 = D2H, 3 = both.  Returns the wall time in ms."""
+        keep = [self._addr(b) for b, _, _ in jobs]
+        ptrs = (C.c_void_p * len(jobs))(*[(k[0] or 0) + int(j[1]) for k, j in zip(keep, jobs)])
+        sizes = (C.c_uint64 * len(jobs))(*[int(j[2]) for j in jobs])
+        outs = (C.c_uint64 * len(jobs))(*[int(x) for x in out_bytes])
+        ms = C.c_double(0)
+        rc = self._lib.bstr_pcie_probe(self._ctx, ptrs, sizes, outs, len(jobs), int(mode), int(reps), C.byref(ms))
+        if rc:
+            self._raise(rc)
+        return ms.value
+
     def stats(self):
         st = Stats()
         self._lib.bstr_get_stats(self._ctx, C.byref(st))
-        return {k: getattr(st, k) for k, _ in Stats._fields_}
+        d = {k: getattr(st, k) for k, _ in Stats._fields_}
+        d["device_batches"] = [int(x) for x in st.device_batches]
+        return d
 
     def reset_stats(self):
         self._lib.bstr_reset_stats(self._ctx)

@@ -43,6 +43,7 @@ struct Lane {
     cudaStream_t st;
     cudaEvent_t ev[8];
     int dev;                       // CUDA ordinal
+    int dev_index;                 // index into bstr_params.devices
     const uint8_t *raw;            // host input of the batch in flight
     uint64_t nbytes;
     int final;

@@ -490,7 +490,10 @@ static int decode_run(const uint8_t *in, size_t size, uint64_t bit, uint64_t sto
         at += 8;
         while (at < size && in[at] == 0) at++;                 // zero padding between members (tape blocks); gzip(1) accepts it
         const size_t body = at < size ? gzip_header(in, size, at) : 0;
-        if (!body) {                                            // end of file, or trailing garbage (ignored, as zlib's gzread does)
+        if (!body) {
+            // end of file -- or bytes that are no gzip member: Python's gzip module, which the
+            // reference reads through (fastq.pyx:50-51), raises "Not a gzipped file" for them
+            if (at < size) return strict ? D_REJECT : D_ERROR;
             o.stream_end = true;
             o.end_bit = (uint64_t)size * 8;
             return D_OK;

@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <mutex>
 #include <vector>
 
@@ -38,7 +39,7 @@ static int grow(bstr_ctx *ctx, void **p, size_t *cap, size_t need, bool pinned_h
     if (*cap >= need) return BSTR_OK;
     size_t ncap = need + need / 4 + 4096;
     if (*p) { if (pinned_host) cudaFreeHost(*p); else cudaFree(*p); *p = nullptr; *cap = 0; }
-    cudaError_t e = pinned_host ? cudaHostAlloc(p, ncap, cudaHostAllocDefault) : cudaMalloc(p, ncap);
+    cudaError_t e = pinned_host ? cudaHostAlloc(p, ncap, cudaHostAllocPortable) : cudaMalloc(p, ncap);
     if (e != cudaSuccess) return cuda_fail(ctx, e, pinned_host ? "cudaHostAlloc" : "cudaMalloc", __LINE__);
     *cap = ncap;
     return BSTR_OK;
@@ -61,7 +62,7 @@ int DeviceSlot::reserve(bstr_ctx *ctx, uint64_t nbytes, uint64_t out_need)
     GROW(d_lb, cap_lb, (2 * n_tiles_f + 2) * 8, false);
     if (!d_state) {
         CUDA_TRY(cudaMalloc((void **)&d_state, sizeof(BatchState) + 64));
-        CUDA_TRY(cudaHostAlloc((void **)&h_state, sizeof(BatchState), cudaHostAllocDefault));
+        CUDA_TRY(cudaHostAlloc((void **)&h_state, sizeof(BatchState), cudaHostAllocPortable));
     }
     if (ctx->force_generic) return reserve_generic(ctx, nbytes);
     return BSTR_OK;
@@ -405,7 +406,7 @@ void bstr_reset_stats(bstr_ctx *ctx) { if (ctx) memset(&ctx->stats, 0, sizeof(ct
 void *bstr_host_alloc(size_t nbytes)
 {
     void *p = nullptr;
-    if (cudaHostAlloc(&p, nbytes ? nbytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaHostAlloc(&p, nbytes ? nbytes : 1, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return p;
 }
 void bstr_host_free(void *p) { if (p) cudaFreeHost(p); }

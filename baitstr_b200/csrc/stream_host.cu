@@ -16,6 +16,7 @@
 //                       reference prints the chunks before a bad record)
 #include <errno.h>
 #include <fcntl.h>
+#include <sched.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -61,48 +62,130 @@ void stream_release(bstr_ctx *ctx)
     ctx->engine = nullptr;
 }
 
+// Serial gzip reader (small files, BSTR_SERIAL_INFLATE): zlib's inflate() one member at a time,
+// with the member chain of Python's gzip module, which the reference reads through
+// (fastq.pyx:50-51): members may follow each other, zero padding after a member is skipped,
+// anything else after a member -- and a file that does not start with a gzip header -- is an
+// error ("Not a gzipped file").  zlib's own gzread() would accept both silently.
+struct GzSerial {
+    int fd = -1;
+    z_stream zs;
+    bool zs_live = false, in_member = false, eof = false, any_member = false;
+    uint32_t crc = 0, isize = 0;
+    std::vector<uint8_t> ibuf;
+    const char *err = nullptr;
+    bool open_fd(int f) { fd = f; ibuf.resize(1 << 20); memset(&zs, 0, sizeof(zs)); return true; }
+    bool refill()
+    {
+        if (zs.avail_in) return true;
+        for (;;) {
+            ssize_t r = read(fd, ibuf.data(), ibuf.size());
+            if (r < 0 && errno == EINTR) continue;
+            if (r < 0) { err = strerror(errno); return false; }
+            zs.next_in = ibuf.data(); zs.avail_in = (uInt)r;
+            return true;                                          // avail_in == 0: end of file
+        }
+    }
+    int get_byte()                                                // -1: end of file, -2: read error
+    {
+        if (!refill()) return -2;
+        if (!zs.avail_in) return -1;
+        zs.avail_in--;
+        return *zs.next_in++;
+    }
+    // gzip member header as gzip.py reads it (_read_gzip_header): magic, method 8, flags, the
+    // optional fields skipped; the header CRC is read and NOT checked, as there.
+    bool read_header(int first)
+    {
+        uint8_t h[10];
+        h[0] = (uint8_t)first;
+        for (int i = 1; i < 10; i++) { const int c = get_byte(); if (c < 0) { if (c == -1) err = i < 2 ? "not a gzip file" : "truncated gzip header"; return false; } h[i] = (uint8_t)c; }
+        if (h[0] != 0x1f || h[1] != 0x8b) { err = any_member ? "not a gzip file (bytes after the last member)" : "not a gzip file"; return false; }
+        if (h[2] != 8) { err = "unknown compression method"; return false; }
+        const int flg = h[3];
+        auto skip = [&](int n) { while (n-- > 0) if (get_byte() < 0) { if (!err) err = "truncated gzip header"; return false; } return true; };
+        auto skipz = [&]() { for (;;) { const int c = get_byte(); if (c < 0) { if (!err) err = "truncated gzip header"; return false; } if (c == 0) return true; } };
+        if (flg & 4) { const int lo = get_byte(), hi = get_byte(); if (lo < 0 || hi < 0) { if (!err) err = "truncated gzip header"; return false; } if (!skip(lo | hi << 8)) return false; }
+        if ((flg & 8) && !skipz()) return false;
+        if ((flg & 16) && !skipz()) return false;
+        if ((flg & 2) && !skip(2)) return false;
+        return true;
+    }
+    long read_some(uint8_t *dst, size_t want)                     // bytes (0 = EOF) or -1
+    {
+        if (want > (1u << 30)) want = 1u << 30;
+        size_t got = 0;
+        while (got < want && !eof) {
+            if (!in_member) {
+                // between members: skip zero padding, then a member must start (or the file ends)
+                int c;
+                do c = get_byte(); while (c == 0 && any_member);
+                if (c == -2) return -1;
+                if (c == -1) { eof = true; break; }
+                if (!read_header(c)) return -1;
+                if (zs_live) inflateReset2(&zs, -15);
+                else if (inflateInit2(&zs, -15) != Z_OK) { err = "zlib initialisation failed"; return -1; }
+                zs_live = true; in_member = true; crc = 0; isize = 0;
+            }
+            if (!refill()) return -1;
+            if (!zs.avail_in) { err = "compressed file ended before the end-of-stream marker was reached"; return -1; }
+            zs.next_out = dst + got; zs.avail_out = (uInt)(want - got);
+            const int r = inflate(&zs, Z_NO_FLUSH);
+            const size_t now = want - zs.avail_out;
+            crc = (uint32_t)crc32(crc, dst + got, (uInt)(now - got));
+            isize += (uint32_t)(now - got);
+            got = now;
+            if (r == Z_STREAM_END) {
+                uint8_t t[8];
+                for (int i = 0; i < 8; i++) { const int c = get_byte(); if (c < 0) { if (!err) err = "compressed file ended before the end-of-stream marker was reached"; return -1; } t[i] = (uint8_t)c; }
+                const uint32_t want_crc = t[0] | t[1] << 8 | t[2] << 16 | (uint32_t)t[3] << 24, want_len = t[4] | t[5] << 8 | t[6] << 16 | (uint32_t)t[7] << 24;
+                if (want_crc != crc) { err = "CRC check failed"; return -1; }
+                if (want_len != isize) { err = "incorrect length check"; return -1; }
+                in_member = false; any_member = true;
+                continue;
+            }
+            if (r == Z_OK || (r == Z_BUF_ERROR && zs.avail_in == 0)) continue;
+            err = zs.msg ? zs.msg : "corrupt gzip data";
+            return -1;
+        }
+        return (long)got;
+    }
+    void close_all() { if (zs_live) inflateEnd(&zs); zs_live = false; if (fd >= 0) close(fd); fd = -1; }
+};
+
 struct Source {
     int fd = -1;
-    gzFile gz = nullptr;
+    GzSerial gz;
     bool is_gz = false;
     int open_path(const char *path)
     {
         const size_t n = strlen(path);
         is_gz = n >= 3 && strcmp(path + n - 3, ".gz") == 0;          // fastq.pyx:50
-        if (is_gz) {
-            gz = gzopen(path, "rb");
-            if (!gz) return -1;
-            gzbuffer(gz, 1 << 20);
-        } else {
-            fd = open(path, O_RDONLY);
-            if (fd < 0) return -1;
+        fd = open(path, O_RDONLY);
+        if (fd < 0) return -1;
 #ifdef POSIX_FADV_SEQUENTIAL
-            posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+        posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
 #endif
-        }
+        if (is_gz) { gz.open_fd(fd); fd = -1; }
         return 0;
     }
     // returns bytes read (0 = EOF) or -1
     long read_some(uint8_t *dst, size_t want)
     {
         if (want > (1u << 30)) want = 1u << 30;
-        if (is_gz) {
-            int r = gzread(gz, dst, (unsigned)want);
-            if (r < 0) return -1;
-            if (r == 0 && !gzeof(gz)) return -1;
-            return r;
-        }
+        if (is_gz) return gz.read_some(dst, want);
         for (;;) {
             ssize_t r = read(fd, dst, want);
             if (r < 0 && errno == EINTR) continue;
             return (long)r;
         }
     }
+    const char *error() const { return is_gz ? gz.err : nullptr; }
     void close_all()
     {
-        if (gz) gzclose(gz);
+        gz.close_all();
         if (fd >= 0) close(fd);
-        gz = nullptr; fd = -1;
+        fd = -1;
     }
 };
 
@@ -186,7 +269,8 @@ static PinnedBuf get_buf(Pipeline &P)
             lk.unlock();
             PinnedBuf b{nullptr, P.buf_cap};
             const double t0 = now_ms();
-            if (cudaHostAlloc((void **)&b.p, b.cap, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); b.p = nullptr; b.cap = 0; }
+            if (cudaHostAlloc((void **)&b.p, b.cap, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); b.p = nullptr; b.cap = 0; }
+            lk.lock();
             P.t_alloc += now_ms() - t0;
             return b;
         }
@@ -354,7 +438,7 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
                     j->off = HEAD - tail.size();
                 } else {                                 // a record longer than HEAD: one-off buffer
                     PinnedBuf big{nullptr, tail.size() + cut + 1};
-                    if (big.cap > (2ull << 30) || cudaHostAlloc((void **)&big.p, big.cap, cudaHostAllocDefault) != cudaSuccess) {
+                    if (big.cap > (2ull << 30) || cudaHostAlloc((void **)&big.p, big.cap, cudaHostAllocPortable) != cudaSuccess) {
                         cudaGetLastError(); errno = ENOMEM;
                         fail(g.buf, "record too large reading"); break;
                     }
@@ -393,8 +477,8 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
             const double t0 = now_ms();
             sg.failed = !src.fill(off, len, b.p + HEAD, &sg.len, &sg.lines, &sg.info);
             const double t1 = now_ms();
+            { std::lock_guard<std::mutex> g(P.mu); P.t_read += t1 - t0; }
             std::lock_guard<std::mutex> g(mu);
-            P.t_read += t1 - t0;
             segs[k] = std::move(sg);
             advance();
         }
@@ -462,16 +546,20 @@ static void reader_main(Pipeline *pp)
             while (!eof && have < b.cap) {
                 errno = 0;
                 long r = src.read_some(b.p + have, b.cap - have);
-                if (r < 0) { reader_fail(P, fi, b, "read error on", P.paths[fi]); b.p = nullptr; stop = true; break; }
+                if (r < 0) {
+                    if (src.error()) errno = 0;
+                    reader_fail(P, fi, b, "read error on", P.paths[fi], src.error());
+                    b.p = nullptr; stop = true; break;
+                }
                 if (r == 0) eof = true;
                 have += (size_t)r;
             }
-            P.t_read += now_ms() - tr0;
+            { std::lock_guard<std::mutex> g(P.mu); P.t_read += now_ms() - tr0; }
             if (stop) break;
             if (eof) { emit(P, new_job(fi, b, have, true, true)); b.p = nullptr; break; }
             const double tc0 = now_ms();
             const size_t cut = record_cut(b.p, have);
-            P.t_cut += now_ms() - tc0;
+            { std::lock_guard<std::mutex> g(P.mu); P.t_cut += now_ms() - tc0; }
             if (cut == 0) {
                 // not even one whole record in a full buffer: continue in a larger one-off buffer
                 if (b.cap >= (2ull << 30)) {
@@ -481,7 +569,7 @@ static void reader_main(Pipeline *pp)
                     emit(P, j); b.p = nullptr; stop = true; break;
                 }
                 PinnedBuf nb{nullptr, b.cap * 2 > (2ull << 30) ? (size_t)(2ull << 30) : b.cap * 2};
-                if (cudaHostAlloc((void **)&nb.p, nb.cap, cudaHostAllocDefault) != cudaSuccess) {
+                if (cudaHostAlloc((void **)&nb.p, nb.cap, cudaHostAllocPortable) != cudaSuccess) {
                     cudaGetLastError(); errno = ENOMEM;
                     reader_fail(P, fi, b, "out of page-locked memory reading", P.paths[fi]); b.p = nullptr; stop = true; break;
                 }
@@ -602,8 +690,15 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     P.ctx = ctx; P.paths = paths; P.npaths = npaths;
     P.buf_cap = ctx->p.batch_bytes;
     auto knob = [](const char *name, int dflt) { const char *v = getenv(name); return v && atoi(v) > 0 ? atoi(v) : dflt; };
-    P.n_readers = ctx->p.host_threads > 4 ? (ctx->p.host_threads > 32 ? 32 : ctx->p.host_threads) : 4;
-    P.plain_readers = knob("BSTR_PLAIN_READERS", P.n_readers >= 8 ? 8 : 4);  // pread + newline count: memory-bound
+    int host_threads = ctx->p.host_threads;
+    if (host_threads <= 0) {                                   // automatic: the CPUs this process may run on
+        cpu_set_t cs;
+        host_threads = sched_getaffinity(0, sizeof(cs), &cs) == 0 ? CPU_COUNT(&cs) : 4;
+    }
+    P.n_readers = host_threads > 4 ? (host_threads > 64 ? 64 : host_threads) : 4;
+    // pread + newline count is memory-bound: 8 threads feed one GPU's PCIe share; more GPUs get more
+    const int want_plain = 8 * ctx->p.n_devices;
+    P.plain_readers = knob("BSTR_PLAIN_READERS", P.n_readers >= want_plain ? want_plain : (P.n_readers >= 8 ? P.n_readers : 4));
     P.gz_fillers = knob("BSTR_GZ_FILLERS", P.n_readers >= 8 ? 3 : 2);        // resolve markers, CRC-32, newline count
     P.gz_decoders = knob("BSTR_GZ_DECODERS", P.n_readers - P.gz_fillers);    // together they use the host threads allowed
     P.gz_pending = knob("BSTR_GZ_PENDING", 6);
@@ -677,7 +772,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     for (auto &b : P.free_bufs) ctx->engine->pool.push_back(b);
     for (int l = 0; l < ctx->n_lanes; l++) ctx->lanes[l].busy = false;
     CUDA_TRY(cudaSetDevice(ctx->dev));
-    ctx->stats.wall_ms += now_ms() - t_begin;
+    { std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock); ctx->stats.wall_ms += now_ms() - t_begin; }
     if (getenv("BSTR_TRACE"))
         fprintf(stderr, "[bstr] run_files %.1f ms: lanes %.1f | reader: read %.1f cut %.1f pinned-alloc %.1f buffer-wait %.1f | "
                 "writer: wait %.1f write %.1f | device: h2d %.1f kernels %.1f d2h %.1f (summed over %llu batches)\n",
@@ -694,6 +789,26 @@ extern "C" int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t r
                            uint64_t *stats6, char *err, size_t errlen)
 {
     auto say = [&](const char *m) { if (err && errlen) snprintf(err, errlen, "%s", m); };
+    if (threads <= 0) {                                   // the serial reader of small files (GzSerial)
+        Source src;
+        if (src.open_path(path) != 0) { say(strerror(errno)); return BSTR_ERR_IO; }
+        src.is_gz = true;
+        if (src.fd >= 0) { src.gz.open_fd(src.fd); src.fd = -1; }
+        std::vector<uint8_t> buf(1 << 20);
+        uint64_t total = 0;
+        int rc = 0;
+        for (;;) {
+            const long r = src.read_some(buf.data(), buf.size());
+            if (r < 0) { say(src.error() ? src.error() : "read error"); rc = BSTR_ERR_IO; break; }
+            if (r == 0) break;
+            total += (uint64_t)r;
+            if (out_fd >= 0 && write_all(out_fd, buf.data(), (size_t)r) != 0) { say(strerror(errno)); rc = BSTR_ERR_IO; break; }
+        }
+        src.close_all();
+        struct stat sb0;
+        if (stats6) { memset(stats6, 0, 6 * sizeof(uint64_t)); stats6[0] = stat(path, &sb0) == 0 ? (uint64_t)sb0.st_size : 0; stats6[1] = total; }
+        return rc;
+    }
     const int fd = open(path, O_RDONLY);
     struct stat sb;
     if (fd < 0 || fstat(fd, &sb) != 0) { say(strerror(errno)); if (fd >= 0) close(fd); return BSTR_ERR_IO; }

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define BSTR_ABI_VERSION 1
+#define BSTR_ABI_VERSION 2
 
 /* error codes (negative return values) */
 enum {
@@ -83,6 +83,7 @@ typedef struct bstr_stats {
     uint64_t records, selected, in_bytes, out_bytes, batches;
     uint64_t fallback_batches;                     /* batches re-run through the generic kernels */
     double h2d_ms, kernel_ms, d2h_ms, wall_ms;     /* summed over batches (CUDA events)      */
+    uint64_t device_batches[16];                   /* batches collected per entry of params.devices */
 } bstr_stats;
 
 /* result of the device-resident benchmark loop */
@@ -157,6 +158,16 @@ uint32_t bstr_debug_codes_cap(const bstr_ctx *ctx, uint32_t read_length);
 int bstr_bench_resident(bstr_ctx *ctx, const uint8_t *const *raws, const uint64_t *nbytes,
                         int nbatches, int steps, int warmup, int flush_l2, bstr_bench_out *out);
 
+/* Copy-only probe of the host<->device path that the lanes use (no kernels): the jobs
+ * (raws[i], nbytes[i]) are dealt to the context's lanes exactly as bench.py's end-to-end leg
+ * deals its sub-batches (lane i % bstr_lanes(), at most one job per lane in flight, wait for
+ * the oldest before re-using its lane).  mode bit 0: copy the input host -> device; bit 1:
+ * copy out_bytes[i] bytes device -> page-locked host (after the lane's H2D completed, as
+ * bstr_collect_batch does).  One cudaMemcpyAsync per copy.  *ms = host wall time of `reps`
+ * passes.  Names the ceiling of the end-to-end numbers; no counterpart in the reference. */
+int bstr_pcie_probe(bstr_ctx *ctx, const uint8_t *const *raws, const uint64_t *nbytes,
+                    const uint64_t *out_bytes, int njobs, int mode, int reps, double *ms);
+
 /* Page-locked host memory for callers that want their batches DMA'd without a staging
  * copy (bench.py's end-to-end leg).  Plain malloc'd buffers work too, only slower. */
 void *bstr_host_alloc(size_t nbytes);
@@ -179,7 +190,10 @@ int bstr_geometry_probe(double record_bytes, int window_words, uint32_t out[8]);
  * range_bytes: compressed bytes per decoder work item; seg_bytes: inflated bytes per output
  * segment.  stats6 (may be NULL): in bytes, out bytes, ranges searched, runs accepted, runs
  * decoded again from the true position, gzip members.  0, or BSTR_ERR_IO with a message in err
- * (not gzip, corrupt deflate data, CRC-32/ISIZE mismatch, truncated file). */
+ * (not gzip, corrupt deflate data, CRC-32/ISIZE mismatch, truncated file, bytes after the last
+ * member that are neither zero padding nor another member -- Python's gzip module rejects those
+ * too).  threads <= 0 selects the serial zlib-based reader that bstr_run_files uses for small
+ * files; both readers accept and reject the same files. */
 int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes, uint64_t seg_bytes,
                 uint64_t *stats6, char *err, size_t errlen);
 

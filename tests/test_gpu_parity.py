@@ -569,6 +569,60 @@ def test_run_files_parallel_readers_stop_on_bad_record(capi, tmp_path):
         assert open(outp, "rb").read() == oracle.select_buffer(a)
 
 
+def test_multi_gpu_run_files_byte_identical(capi, tmp_path):
+    """The in-process multi-GPU path (bstr_params.n_devices > 1: one device thread per GPU, batches
+    dealt to whichever GPU has a free lane, ordered writer) against the 1-device run and the
+    oracle: plain and .gz shards, default and tiny batches, a bad record in a late shard.
+    Replaces Pool + ordered print of /root/reference/src/select_STR_reads.pyx:356-367.  Skips on a
+    1-GPU box; run it with `gpurun --gpus 2`."""
+    import gzip
+    ndev = capi.device_count()
+    if ndev < 2:
+        pytest.skip("needs >= 2 GPUs (gpurun --gpus 2)")
+    ndev = min(ndev, 8)
+    shards = [util.synth_fastq(30000 + 1000 * i, 100 + 25 * (i % 3), seed=900 + i, tag="s%d" % i, p_str=0.5) for i in range(ndev + 1)]
+    plain, gz = [], []
+    for i, raw in enumerate(shards):
+        pth = str(tmp_path / ("shard%d.fq" % i))
+        open(pth, "wb").write(raw)
+        plain.append(pth)
+        open(pth + ".gz", "wb").write(gzip.compress(raw, 1))
+        gz.append(pth + ".gz")
+    want = b"".join(oracle.select_buffer(r) for r in shards)
+    done = "".join("Done processing %s\n" % q for q in plain)
+    devs = list(range(ndev))
+    for files, bb in ((plain, 0), (plain, 256 << 10), (gz, 4 << 20), (plain, 4 << 20)):
+        outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+        with capi.Context(devices=devs, batch_bytes=bb, host_threads=8) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            assert ctx.lanes() == 3 * ndev
+            ctx.run_files(files, out_fd=fo.fileno(), err_fd=fe.fileno())
+            st = ctx.stats()
+        assert open(outp, "rb").read() == want, (files[0], bb)
+        if files is plain:
+            assert open(errp).read() == done
+        assert sum(st["device_batches"]) == st["batches"]
+        if bb == 256 << 10:                                   # ~ 30 batches per shard: every GPU must have had work
+            assert all(n > 0 for n in st["device_batches"][:ndev]), st["device_batches"]
+    # the lanes API on several devices: lane l lives on device l % ndev
+    with capi.Context(devices=devs) as ctx:
+        nl = ctx.lanes()
+        keep = [ctx.submit(l, shards[l % len(shards)]) for l in range(nl)]
+        for l in range(nl):
+            assert ctx.collect(l)[0] == oracle.select_buffer(shards[l % len(shards)])
+    # a bad record in the last shard: everything before its batch is written, the error names it
+    lines = shards[-1].split(b"\n")
+    lines[4 * 20000 + 2] = b"-"
+    open(plain[-1], "wb").write(b"\n".join(lines))
+    outp = str(tmp_path / "o2.fq")
+    with capi.Context(devices=devs, batch_bytes=256 << 10) as ctx, open(outp, "wb") as fo:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files(plain, out_fd=fo.fileno(), err_fd=-1)
+        assert ei.value.code == -12 and "record 20000" in str(ei.value)
+    got = open(outp, "rb").read()
+    head = b"".join(oracle.select_buffer(r) for r in shards[:-1])
+    assert got.startswith(head) and want.startswith(got[:len(head)]) and len(got) < len(want)
+
+
 def test_module_level_api_reads_like_the_reference(capi, capsys):
     """baitstr_b200.select_STR_reads mirrors the reference module (select_STR_reads.pyx:106,171,
     187,294): same call shapes and return tuples, so the reference's own call sites work

@@ -92,9 +92,37 @@ def test_header_fields_padding_and_trailing_garbage(tmp_path, fastq):
     z = hdr + c.compress(body) + c.flush() + struct.pack("<II", zlib.crc32(body), len(body))
     for cfg in CONFIGS[:2]:
         assert inflate(tmp_path, z, *cfg)[0] == body
-    # zero padding, then a second member; trailing bytes that are not gzip are ignored (zlib's gzread does the same)
-    z2 = z + b"\0" * 700 + gzip.compress(fastq[2_000_000:2_500_000], 6, mtime=0) + b"trailing junk, not gzip" * 9
-    assert inflate(tmp_path, z2, 3, 65536, 1000000)[0] == fastq[:2_500_000]
+    # zero padding, then a second member, then more zero padding: accepted (as Python's gzip module does)
+    z2 = z + b"\0" * 700 + gzip.compress(fastq[2_000_000:2_500_000], 6, mtime=0)
+    assert gzip.decompress(z2 + b"\0" * 33) == fastq[:2_500_000]
+    for threads in (3, 0):                                   # the parallel inflater and the serial reader of small files
+        assert inflate(tmp_path, z2 + b"\0" * 33, threads, 65536, 1000000)[0] == fastq[:2_500_000]
+    # bytes after the last member that are no gzip member: the reference's gzip.open raises
+    # ("Not a gzipped file"), so do both readers -- whatever the size of the file
+    junk = z2 + b"trailing junk, not gzip" * 9
+    with pytest.raises(Exception):
+        gzip.decompress(junk)
+    for threads in (3, 0):
+        p = str(tmp_path / "junk.gz")
+        open(p, "wb").write(junk)
+        with pytest.raises(capi.BstrError):
+            capi.gunzip(p, -1, threads, 65536, 1000000)
+
+
+def test_serial_reader_matches_parallel(tmp_path, fastq):
+    """threads = 0: the zlib-based reader bstr_run_files uses for small files."""
+    cases = [gzip.compress(fastq[:300000], 6, mtime=0),
+             gzip.compress(fastq[:1000], 1, mtime=0) + gzip.compress(fastq[1000:5000], 9, mtime=0),
+             gzip.compress(b"", 6, mtime=0)]
+    for z in cases:
+        assert inflate(tmp_path, z, 0, 65536, 1000000)[0] == gzip.decompress(z)
+    good = gzip.compress(fastq[:300000], 6, mtime=0)
+    crc = bytearray(good); crc[-6] ^= 1
+    for bad in (good[:len(good) // 2], bytes(crc), fastq[:100000], good[:12]):
+        p = str(tmp_path / "bad.gz")
+        open(p, "wb").write(bad)
+        with pytest.raises(capi.BstrError):
+            capi.gunzip(p, -1, 0)
 
 
 def test_errors_are_loud(tmp_path, fastq):

@@ -5,7 +5,7 @@
 #     -o ../libbaitstr_select_occ3.so /tmp/occ3.o stream_host.o pinflate.o -lz -lpthread -cudart shared
 # occupancy experiment: phases A-E only (BSTR_EXP 4|8 = no format, no flush; +16 = dummy stage) at 2 / 3 CTAs per SM
 run() { # label, lib, exp, geom
-  BSTR_LIB=$2 BSTR_EXP=$3 BSTR_GEOM=$4 python bench.py --reads 4000000 --steps 3 --warmup 3 --no-cpu --no-ingest 2>/dev/null | python -c "
+  BSTR_LIB=$2 BSTR_EXP=$3 BSTR_GEOM=$4 python bench.py --reads 4000000 --steps 3 --warmup 3 --quick 2>/dev/null | python -c "
 import sys,json
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', 'lib=$(basename $2)', 'exp=$3 geom=$4', 'ms/step', d['ms_per_step'], 'reads/s %.4g' % d['value'], 'kernel_us', d['roofline']['kernel_us_per_launch'])"
 }
