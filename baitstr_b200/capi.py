@@ -14,7 +14,11 @@ ABI_VERSION = 2
 
 def library_path():
     # BSTR_LIB: another build of the same library (kernel A/B measurements only)
-    return os.environ.get("BSTR_LIB") or os.path.join(HERE, "libbaitstr_select.so")
+    if os.environ.get("BSTR_LIB"):
+        return os.environ["BSTR_LIB"]
+    here = os.path.join(HERE, "libbaitstr_select.so")
+    up = os.path.join(os.path.dirname(HERE), "libbaitstr_select.so")     # installed layout: bin/libbaitstr_select.so
+    return here if os.path.exists(here) or not os.path.exists(up) else up
 
 
 class Params(C.Structure):

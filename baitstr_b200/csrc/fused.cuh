@@ -70,6 +70,10 @@ inline TileGeom make_geometry(uint32_t tile, uint32_t threads, uint32_t stage)
     TileGeom g;
     g.threads = threads; g.tile = tile; g.region = tile + FT_OVL; g.chunks = g.region / 16;
     g.cpt = (g.chunks + threads - 1) / threads;
+    // a thread indexes cpt CONTIGUOUS 16-byte chunks, so the lanes of a quarter warp load chunks
+    // cpt apart: an odd stride spreads them over all eight 16-byte bank groups, an even one over
+    // four or fewer (4-way conflict on every LDS.128 of the index phase)
+    if (!(g.cpt & 1u) && g.cpt < (uint32_t)FT_MAXCPT) g.cpt++;
     g.recmax = 2 * threads; g.nlmax = 5 * g.recmax + 64; g.stage = stage;
     uint32_t o = (sizeof(FusedVars) + 15) & ~15u;
     g.off_in = o;       o += 16 + g.region + 32;
@@ -310,6 +314,135 @@ __device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileG
     return cnt;
 }
 
+// ---- per-warp work list of the matcher (matcher.cuh: first_trip / extend_trips) -----------------
+// The (read, period) pairs of a record warp whose copy-count scan continues are parked in shared
+// memory and run lane-per-pair, 32 at a time after the last period, so the loop over copy numbers is executed by full
+// warps once instead of once per period by the few lanes that hold a long repeat.  Results come
+// back through a key (K*c << 16 | c << 3 | K: the tuple order of take_if_better) and a candidate
+// mask per owner lane and strand.  The list lives in the staging buffer, which nothing else uses
+// before phase F.
+template <int W> struct WarpWork {
+    static constexpr int ITEM_WORDS = W + 1, CAP = 160;   // 5 periods x 32 lanes: the list cannot overflow
+    static constexpr int WORDS = CAP * ITEM_WORDS + 64 + 64 * W;   // items, 2 x 32 keys, 2 x 32 x W candidates
+    uint32_t *items, *key, *cand;
+    int count;                                              // warp-uniform
+    __device__ __forceinline__ void init(uint32_t *base)
+    {
+        items = base; key = base + CAP * ITEM_WORDS; cand = key + 64; count = 0;
+    }
+    __device__ __forceinline__ void reset_keys()
+    {
+        const int lane = threadIdx.x & 31;
+        key[lane] = 0; key[32 + lane] = 0;
+        __syncwarp();
+    }
+    // run the top nitems (<= 32) pairs of the list, one per lane
+    __device__ __forceinline__ void run(int nitems)
+    {
+        const int lane = threadIdx.x & 31;
+        __syncwarp();
+        const bool has = lane < nitems;
+        Deferred<W> d;
+        int cf = 0, cr = 0;
+        Bits<W> df, dr;
+#pragma unroll
+        for (int i = 0; i < W; i++) { d.cur.w[i] = 0; df.w[i] = 0; dr.w[i] = 0; }
+        d.meta = 0;
+        if (has) {
+            const uint32_t *it = items + (count - 1 - lane) * ITEM_WORDS;
+#pragma unroll
+            for (int i = 0; i < W; i++) d.cur.w[i] = it[i];
+            d.meta = it[W];
+            extend_trips<W>(d, cf, df, cr, dr);
+        }
+        const uint32_t owner = d.meta >> 27, K = d.meta & 7u;
+        const uint32_t kf = (K * cf) << 16 | (uint32_t)cf << 3 | K, kr = (K * cr) << 16 | (uint32_t)cr << 3 | K;
+        if (cf) atomicMax(&key[owner], kf);
+        if (cr) atomicMax(&key[32 + owner], kr);
+        __syncwarp();
+        if (cf && key[owner] == kf) {
+#pragma unroll
+            for (int i = 0; i < W; i++) cand[owner * W + i] = df.w[i];
+        }
+        if (cr && key[32 + owner] == kr) {
+#pragma unroll
+            for (int i = 0; i < W; i++) cand[(32 + owner) * W + i] = dr.w[i];
+        }
+        count -= nitems;
+        __syncwarp();
+    }
+    // called by every lane of the warp, once per period
+    __device__ __forceinline__ void push(bool need, const Deferred<W> &d)
+    {
+        const uint32_t lane = threadIdx.x & 31;
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, need);
+        if (!m) return;
+        if (need) {
+            uint32_t *it = items + (count + __popc(m & ((1u << lane) - 1u))) * ITEM_WORDS;
+#pragma unroll
+            for (int i = 0; i < W; i++) it[i] = d.cur.w[i];
+            it[W] = d.meta | lane << 27;
+        }
+        count += __popc(m);
+    }
+    // after the last period: run what is left and fold the results into the owner's candidates
+    __device__ __forceinline__ void finish(ScanState<W> &S)
+    {
+        const int lane = threadIdx.x & 31;
+        while (count) run(count < 32 ? count : 32);
+        const uint32_t kf = key[lane], kr = key[32 + lane];
+        if (kf) {
+            Bits<W> c;
+#pragma unroll
+            for (int i = 0; i < W; i++) c.w[i] = cand[lane * W + i];
+            take_if_better(S.bf, c, (int)(kf & 7u), (int)(kf >> 3 & 0x1FFFu));
+        }
+        if (kr) {
+            Bits<W> c;
+#pragma unroll
+            for (int i = 0; i < W; i++) c.w[i] = cand[(32 + lane) * W + i];
+            take_if_better(S.br, c, (int)(kr & 7u), (int)(kr >> 3 & 0x1FFFu));
+        }
+        __syncwarp();
+    }
+};
+
+// Both strands of the warp's 32 reads with a W-word window; every lane of the warp calls it
+// (L = 0 for a lane without a read).
+template <int W>
+__device__ __forceinline__ void match_read_warp(const uint8_t *seq, int L, const ScanParams &prm, uint32_t *work,
+                                                Hit &fwd, Hit &rc)
+{
+    WarpWork<W> wl;
+    wl.init(work);
+    wl.reset_keys();
+    ScanState<W> S;
+    scan_first<W>(seq, L, prm, S, [&](bool need, const Deferred<W> &d) { wl.push(need, d); });
+    wl.finish(S);
+    scan_finish<W>(S, L, prm, fwd, rc);
+}
+
+// words of shared memory one record warp needs for its work list (widest window compiled in)
+template <int WMAX> __host__ __device__ constexpr uint32_t warp_work_words() { return (uint32_t)WarpWork<(WMAX >= 4 ? 4 : 2)>::WORDS; }
+
+// Dispatch on the window width as match_read (matcher.cuh), with the warp work list.  `wmax` is
+// warp-uniform; reads wider than the compiled windows take the exact byte path inline.
+template <int WMAX>
+__device__ __forceinline__ void match_read_tile(const uint8_t *seq, int L, const ScanParams &prm, int wmax,
+                                                uint32_t *work, Hit &fwd, Hit &rc)
+{
+    if (wmax <= 2) match_read_warp<2>(seq, L, prm, work, fwd, rc);
+    else if (WMAX >= 4 && wmax <= 4) match_read_warp<(WMAX >= 4 ? 4 : 2)>(seq, L, prm, work, fwd, rc);
+    // 6- and 8-word windows keep the continuing pairs inline: with the scan state of such a window
+    // live across the list run the kernel spills (180 / 504 bytes at the 168-register cap)
+    else if (WMAX == 6 && wmax <= 6) match_read_bits<(WMAX == 6 ? 6 : 2)>(seq, L, prm, fwd, rc);
+    else if (WMAX >= 8 && wmax <= 8) match_read_bits<(WMAX >= 8 ? 8 : 2)>(seq, L, prm, fwd, rc);
+    else {
+        fwd.k = rc.k = 0; fwd.copies = rc.copies = fwd.start = rc.start = 0;
+        if (L > 0) match_read_bytes(seq, L, prm, fwd, rc);
+    }
+}
+
 // CTA size limit per instantiation: batches of long reads have few records per tile, so the wide
 // windows run with at most FT_WIDETHREADS threads and may keep 168 registers (the 8-word matcher
 // spilled 344 bytes under the 128-register cap of 256-thread CTAs and ran 1.5x slower for it)
@@ -373,6 +506,7 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     const uint32_t real_own = tot & 0xFFFFu;
     uint32_t cnt_own = real_own + shift, cnt_all = (tot >> 16) + shift;
     bool bail = cnt_all + 2 > g.nlmax;
+    if ((nthr / 32 - 1) * warp_work_words<WMAX>() * 4u > g.stage) bail = true;   // no room for the matcher's work lists
     {
         uint32_t idx = (ex >> 16) + shift;
 #pragma unroll
@@ -467,23 +601,25 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
         }
         for (uint32_t j = nproc + lane; j < g.recmax; j += 32) s_outoff[j] = 0;
     } else {
+        uint32_t *const work = reinterpret_cast<uint32_t *>(stage) + (wid - 1) * warp_work_words<WMAX>();
         for (uint32_t jb = 0; jb < nproc; jb += rthr) {
             const uint32_t j = jb + rtid;
             const bool live = j < nproc;
             RecordLines ln = {};
-            int L = 0;
-            if (live) { ln = tile_record_lines(s_nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1); }
-            const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
-            Hit f, rc;
-            f.k = rc.k = 0; f.copies = rc.copies = f.start = rc.start = 0;
-            bool sel = false;
+            int L = 0, bad = 0;
             if (live) {
-                int bad = 0;
+                ln = tile_record_lines(s_nl, (int)(i0 + 4 * j)); L = (int)(ln.e1 - ln.s1);
                 if (sin[ln.s0] != '@') bad = BAD_HEADER;                       // fastq.pyx:77
                 else if (!(exp_mask & 2) && bases_invalid(sin + ln.s1, L)) bad = BAD_BASES;        // fastq.pyx:81
                 else if (sin[ln.s2] != '+') bad = BAD_SEPARATOR;                // fastq.pyx:86
-                if (!bad && !(exp_mask & 1)) match_read<WMAX>(sin + ln.s1, L, prm, wmax, f, rc);
-                sel = f.k && rc.k;
+            }
+            const int wmax = __reduce_max_sync(0xFFFFFFFFu, (unsigned)window_words(L, prm));
+            Hit f, rc;
+            // every lane of the warp takes part (the work list votes); a lane without a good record scans nothing
+            const int Lm = (live && !bad && !(exp_mask & 1)) ? L : 0;
+            match_read_tile<WMAX>(sin + ln.s1, Lm, prm, wmax, work, f, rc);
+            const bool sel = f.k && rc.k;
+            if (live) {
                 ReadResult o;
                 o.fstart = sel ? f.start : 0; o.rstart = sel ? rc.start : (uint32_t)bad;
                 o.fck = sel ? ((uint32_t)f.copies << 3 | f.k) : 0;

@@ -218,10 +218,18 @@ __device__ __forceinline__ uint32_t record_out_len(uint32_t name_len, uint32_t L
                                                    const Hit &f, const Hit &r)
 {
     uint32_t a = 1 + name_len;                                  // '@' name
+    if (L < 1000u) {
+        // copies, starts and ends are all bounded by the read length: three digits at most
+        const uint32_t fe = f.start + f.k * f.copies, re = r.start + r.k * r.copies;
+        a += 9 + f.k + r.k + 6 +                                // 8 tabs, '\n', two motifs, one digit per number
+             (f.copies >= 10u) + (f.copies >= 100u) + (f.start >= 10u) + (f.start >= 100u) + (fe >= 10u) + (fe >= 100u) +
+             (r.copies >= 10u) + (r.copies >= 100u) + (r.start >= 10u) + (r.start >= 100u) + (re >= 10u) + (re >= 100u);
+    } else {
     a += 1 + f.k + 1 + dec_digits(f.copies) + 1 + dec_digits(f.start) + 1 +
          dec_digits(f.start + f.k * f.copies);
     a += 1 + r.k + 1 + dec_digits(r.copies) + 1 + dec_digits(r.start) + 1 +
          dec_digits(r.start + r.k * r.copies) + 1;              // ... '\n'
+    }
     a += L + 1 + 2 + Q + 1;                                     // seq \n + \n qual \n
     return a;
 }

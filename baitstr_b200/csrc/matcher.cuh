@@ -279,12 +279,31 @@ __device__ __forceinline__ void take_if_better(Best<W> &b, const Bits<W> &cand, 
     if (c && (K * c > b.k * b.c || (K * c == b.k * b.c && c > b.c))) { b.k = K; b.c = c; b.cand = cand; }
 }
 
-template <int K, int W>
-__device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &nm, const Bits<W> &hm,
-                                            bool use_hm, int sh, int end_max, int n,
-                                            Best<W> &bf, Best<W> &br)
+// The copy-count scan of one period is split in two so that a warp does not run as many trips
+// as its longest repeat for every period (measured round 1: a read needs 1.1 trips for K = 2, its
+// warp ran 5.9 -- scan_period executed with 10 of 32 lanes):
+//   first_trip   every lane, no loop: E_K, M(n), the filters, and the exactly-n-copies candidates
+//                of both strands; reports whether any start can still be admissible with more
+//                copies (M(n+1) & lim != 0) -- true for ~0.5 (read, period) pairs per read
+//   extend_trips the loop over c = n+1, n+2, ... for such a pair, period as a run-time value; the
+//                fused kernel collects the pairs of a warp in a shared-memory list and runs them
+//                lane-per-pair (fused.cuh), other callers run it inline
+// Deferred: one (read, period) pair whose scan continues.  meta = K | c << 3 | sh << 12 | end_max << 16
+// (11 bits); the fused kernel's work list keeps the owner lane in bits 27..31.
+template <int W> struct Deferred {
+    Bits<W> cur;           // M(c), filtered
+    uint32_t meta;
+};
+__device__ __forceinline__ uint32_t deferred_meta(int K, int c, int sh, int end_max)
 {
-    if (end_max - sh < K * n) return;
+    return (uint32_t)K | (uint32_t)c << 3 | (uint32_t)sh << 12 | (uint32_t)end_max << 16;
+}
+
+template <int K, int W>
+__device__ __forceinline__ bool first_trip(const Planes<W> &P, const Bits<W> &nm, const Bits<W> &hm,
+                                           bool use_hm, int sh, int end_max, int n,
+                                           Best<W> &bf, Best<W> &br, Deferred<W> &more)
+{
     Bits<W> E;
 #pragma unroll
     for (int i = 0; i < W; i++) {
@@ -315,36 +334,67 @@ __device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &n
         cur.w[i] = ok;
         M2.w[i] &= ok;
     }
-    Bits<W> lim;                                   // s + K*c <= end_max
-    int c = n <= 1 ? 1 : n;
+    const int c = n <= 1 ? 1 : n;
+    Bits<W> lim;                                   // s >= sh and s + K*c <= end_max
     lowmask(lim, end_max - K * c + 1);
-    lim.w[0] &= ~lowmask32(sh);                    // s >= sh (sh <= 6): folded into word 0 below
-    if (n <= 1) {
-        // c = 1: every position is a one-copy match; cur holds them (filtered)
-    } else {
+    const uint32_t lo_keep = ~lowmask32(sh);       // sh <= 6: word 0 only
+    lim.w[0] &= lo_keep;
+    Bits<W> nxt;
+    if (n <= 1) nxt = M2;                          // c = 1: every (filtered) position is a one-copy match
+    else {
         cur = M2;
         for (int cc = 2; cc < n; cc++) { Bits<W> u = cur; and_shr(cur, u, u, K); }
+        and_shr(nxt, cur, cur, K);
     }
-    int cf = 0, cr = 0;
-    Bits<W> df, dr;
+    Bits<W> nl_;
+    shl(nl_, nxt, K);
+    Bits<W> xf, xr;
+    uint32_t af = 0, ar = 0, live = 0;
+    {
+        Bits<W> lim2;                              // the bound for c + 1 copies
+        shr(lim2, lim, K);
+        lim2.w[0] &= lo_keep;
+#pragma unroll
+        for (int i = 0; i < W; i++) {
+            const uint32_t l = lim.w[i];
+            xf.w[i] = cur.w[i] & ~nxt.w[i] & l;
+            xr.w[i] = cur.w[i] & ~nl_.w[i] & l;
+            af |= xf.w[i]; ar |= xr.w[i];
+            live |= nxt.w[i] & lim2.w[i];
+        }
+    }
+    if (af) take_if_better(bf, xf, K, c);
+    if (ar) take_if_better(br, xr, K, c);
+    more.cur = nxt;
+    more.meta = deferred_meta(K, c + 1, sh, end_max);
+    return live != 0;
+}
+
+// Trips c, c+1, ... of one period from M(c) (meta: deferred_meta).  cf / cr = the largest copy
+// number with an admissible start on the forward / reverse strand (0: none), df / dr those starts.
+template <int W>
+__device__ __forceinline__ void extend_trips(const Deferred<W> &d, int &cf, Bits<W> &df, int &cr, Bits<W> &dr)
+{
+    const int K = (int)(d.meta & 7u), sh = (int)(d.meta >> 12 & 15u), end_max = (int)(d.meta >> 16 & 0x7FFu);   // bits 27..31: the owner lane of a listed pair
+    int c = (int)(d.meta >> 3 & 511u);
+    Bits<W> cur = d.cur, lim;
+    lowmask(lim, end_max - K * c + 1);
+    const uint32_t lo_keep = ~lowmask32(sh);
+    lim.w[0] &= lo_keep;
+    cf = 0; cr = 0;
 #pragma unroll
     for (int i = 0; i < W; i++) { df.w[i] = 0; dr.w[i] = 0; }
-    const uint32_t lo_keep = ~lowmask32(sh);
     for (;;) {
-        if (W <= 4) {
-            // starts that can still be admissible with c or more copies (lim only shrinks with c
-            // and is empty once K * c > end_max - sh).  Testing cur alone keeps a lane in the loop
-            // on repeats outside the admissible range -- above all the run of "no symbol" codes
-            // past the window end, which equal each other: (32 W - Gn) / K phantom copies, 7 trips
-            // for K = 2 on a 50-base window.  Measured: +1.3 % (C2) .. +2.5 % (C3, C5); with the
-            // 6-word window the wider test costs more than the trips it saves (-4 % on C4).
-            uint32_t live = 0;
+        // starts that can still be admissible with c or more copies (lim only shrinks with c and is
+        // empty once K * c > end_max - sh).  Testing cur alone would keep a lane in the loop on
+        // repeats outside the admissible range -- above all the run of "no symbol" codes past the
+        // window end, which equal each other
+        uint32_t live = 0;
 #pragma unroll
-            for (int i = 0; i < W; i++) live |= cur.w[i] & lim.w[i];
-            if (!live) break;
-        } else if (!cur.any() || K * c > end_max - sh) break;
+        for (int i = 0; i < W; i++) live |= cur.w[i] & lim.w[i];
+        if (!live) break;
         Bits<W> nxt, nl_;
-        if (c == 1) nxt = M2; else and_shr(nxt, cur, cur, K);
+        and_shr(nxt, cur, cur, K);
         shl(nl_, nxt, K);
         Bits<W> xf, xr;
         uint32_t af = 0, ar = 0;
@@ -365,8 +415,6 @@ __device__ __forceinline__ void scan_period(const Planes<W> &P, const Bits<W> &n
             lim.w[0] &= lo_keep;
         }
     }
-    take_if_better(bf, df, K, cf);
-    take_if_better(br, dr, K, cr);
 }
 
 // Forward winner among `cand` (all same k and copies): greatest motif bytes, then greatest
@@ -425,30 +473,38 @@ __device__ __forceinline__ bool motif_is_homopolymer(const Planes<W> &P, int pos
     return (a == 0 || a == m) && (b == 0 || b == m) && (c == 0 || c == m);
 }
 
-// Both strands of one read with a W-word window.  seq = first base, L = read length.
-template <int W>
-__device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const ScanParams &prm,
-                                                Hit &fwd, Hit &rc)
+// What the owner of a read keeps between the first trips and the winner pick.
+template <int W> struct ScanState {
+    Planes<W> P;
+    Best<W> bf, br;
+    int g0;
+};
+
+// First trips of every period for one read with a W-word window (seq = first base, L = read
+// length; L <= 0 or a window too small for any match: nothing happens, but emit is still called
+// for every period so that a warp may vote inside it).  emit(need, deferred) is called once per
+// period K = 2..6, in that order, by every caller thread; need = the pair continues in
+// extend_trips.
+template <int W, class Emit>
+__device__ __forceinline__ void scan_first(const uint8_t *seq, int L, const ScanParams &prm, ScanState<W> &S, Emit &&emit)
 {
-    fwd.k = 0; rc.k = 0; fwd.copies = rc.copies = fwd.start = rc.start = 0;
     const int fe = prm.altalgo ? prm.f : 0;          // -x: candidates ignore the flanks
     const int g0 = fe > 6 ? fe - 6 : 0;              // window = [g0, L - g0)
     const int Gn = L - 2 * g0;
     const int sh = fe - g0;
     const int end_max = sh + (L - 2 * fe);           // local bound on a candidate's end
     const int n = prm.n < 1 ? 1 : prm.n;
-    if (Gn <= 0 || end_max - sh < 2 * n) return;
+    const bool alive = Gn > 0 && end_max - sh >= 2 * n;
     const bool use_hm = prm.altalgo && prm.rmhm;
-
-    Planes<W> P;
-    Bits<W> nmask;
-    encode_window<W>(seq + g0, Gn, P, nmask);
-    mark_invalid(P, Gn);
-
-    Best<W> bf, br;
-    bf.k = bf.c = br.k = br.c = 0;
+    S.g0 = g0;
+    S.bf.k = S.bf.c = S.br.k = S.br.c = 0;
 #pragma unroll
-    for (int i = 0; i < W; i++) { bf.cand.w[i] = 0; br.cand.w[i] = 0; }
+    for (int i = 0; i < W; i++) { S.bf.cand.w[i] = 0; S.br.cand.w[i] = 0; }
+
+    Bits<W> nmask;
+    encode_window<W>(seq + g0, alive ? Gn : 0, S.P, nmask);
+    mark_invalid(S.P, alive ? Gn : 0);
+    const Planes<W> &P = S.P;
 
     // nm_k = positions whose k-window holds an N; hm_k = positions whose k-window is one symbol
     Bits<W> nm = nmask, hm, E1;
@@ -471,31 +527,62 @@ __device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const
         shr(t_, nmask, (K) - 1);                                                    \
         _Pragma("unroll") for (int i = 0; i < W; i++) nm.w[i] |= t_.w[i];           \
         if (use_hm && (K) > 2) { Bits<W> h_ = hm; and_shr(hm, h_, E1, (K) - 2); }   \
-        if (prm.kmask & (1 << (K))) scan_period<K, W>(P, nm, hm, use_hm, sh, end_max, n, bf, br); \
+        Deferred<W> d_;                                                             \
+        bool need_ = false;                                                         \
+        if (alive && (prm.kmask & (1 << (K))) && end_max - sh >= (K) * n)           \
+            need_ = first_trip<K, W>(P, nm, hm, use_hm, sh, end_max, n, S.bf, S.br, d_); \
+        emit(need_, d_);                                                            \
     }
     BSTR_PERIOD(2) BSTR_PERIOD(3) BSTR_PERIOD(4) BSTR_PERIOD(5) BSTR_PERIOD(6)
 #undef BSTR_PERIOD
+}
 
-    if (bf.k == 0) return;                           // ProcessSequence: forward None -> drop
+// The winners of both strands from the candidates collected in S (after every deferred pair of
+// the read has been folded into S.bf / S.br with take_if_better).
+template <int W>
+__device__ __forceinline__ void scan_finish(const ScanState<W> &S, int L, const ScanParams &prm, Hit &fwd, Hit &rc)
+{
+    fwd.k = 0; rc.k = 0; fwd.copies = rc.copies = fwd.start = rc.start = 0;
+    const Planes<W> &P = S.P;
+    const int g0 = S.g0;
+    if (S.bf.k == 0) return;                         // ProcessSequence: forward None -> drop
     {
-        const int pos = pick_forward(P, bf.cand, bf.k);
-        const int start = g0 + pos, len = bf.k * bf.c;
+        const int pos = pick_forward(P, S.bf.cand, S.bf.k);
+        const int start = g0 + pos, len = S.bf.k * S.bf.c;
         if (!prm.altalgo) {                          // -x: tests on the winner only (pyx:153-167)
             if (start < prm.f || L - (start + len) < prm.f) return;
-            if (prm.rmhm && motif_is_homopolymer(P, pos, bf.k)) return;
+            if (prm.rmhm && motif_is_homopolymer(P, pos, S.bf.k)) return;
         }
-        fwd.k = bf.k; fwd.copies = bf.c; fwd.start = start;
+        fwd.k = S.bf.k; fwd.copies = S.bf.c; fwd.start = start;
     }
-    if (br.k == 0) return;
+    if (S.br.k == 0) return;
     {
-        const int pos = pick_reverse(P, br.cand, br.k);
-        const int len = br.k * br.c, rstart = L - (g0 + pos + len);
+        const int pos = pick_reverse(P, S.br.cand, S.br.k);
+        const int len = S.br.k * S.br.c, rstart = L - (g0 + pos + len);
         if (!prm.altalgo) {
             if (rstart < prm.f || g0 + pos < prm.f) return;
-            if (prm.rmhm && motif_is_homopolymer(P, pos, br.k)) return;
+            if (prm.rmhm && motif_is_homopolymer(P, pos, S.br.k)) return;
         }
-        rc.k = br.k; rc.copies = br.c; rc.start = rstart;
+        rc.k = S.br.k; rc.copies = S.br.c; rc.start = rstart;
     }
+}
+
+// Both strands of one read with a W-word window, the continuing pairs run inline (callers
+// without a warp work list: k_match_reads, the staged kernels, the host emulation of the tests).
+template <int W>
+__device__ __forceinline__ void match_read_bits(const uint8_t *seq, int L, const ScanParams &prm,
+                                                Hit &fwd, Hit &rc)
+{
+    ScanState<W> S;
+    scan_first<W>(seq, L, prm, S, [&](bool need, const Deferred<W> &d) {
+        if (!need) return;
+        int cf, cr;
+        Bits<W> df, dr;
+        extend_trips<W>(d, cf, df, cr, dr);
+        take_if_better(S.bf, df, (int)(d.meta & 7u), cf);
+        take_if_better(S.br, dr, (int)(d.meta & 7u), cr);
+    });
+    scan_finish<W>(S, L, prm, fwd, rc);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -696,6 +783,21 @@ __device__ __forceinline__ uint32_t swar_invalid(uint32_t w)
     return c | d | e | s7;
 }
 
+// Bit 0 of every byte lane is set iff that byte is NOT one of acgtACGT -- the cheap test (9 ops per
+// 4 bases instead of 22): bits 7,6,3 must read 0,1,0 (bit 5 = case is ignored) and, of the
+// remaining bits, b4 = 0 needs b0 & (b1 | ~b2) (A 001, C 011, G 111) and b4 = 1 needs b2 & ~b1 & ~b0
+// (T 100).  Exactly eight byte values pass, all of them valid.  N, n and '.' fail it and go through
+// swar_invalid.
+__device__ __forceinline__ uint32_t swar_not_acgt(uint32_t w)
+{
+    const uint32_t s1 = w >> 1, s2 = w >> 2, s4 = w >> 4;
+    const uint32_t t = w & (s1 | ~s2);
+    const uint32_t g = s2 & ~s1 & ~w;
+    const uint32_t okbit = (s4 & g) | (~s4 & t);
+    const uint32_t hi = (w ^ 0x40404040u) & 0xC8C8C8C8u;           // bits 7, 6, 3 differ from 0, 1, 0
+    return (~okbit & 0x01010101u) | hi;                            // any bit set: some byte is not ACGT/acgt
+}
+
 // Any byte of [p, p+L) outside acgtnACGTN. ?  Reads whole aligned words around the range.
 __device__ __forceinline__ bool bases_invalid(const uint8_t *p, int L)
 {
@@ -707,15 +809,20 @@ __device__ __forceinline__ bool bases_invalid(const uint8_t *p, int L)
     const uint32_t mfirst = 0xFFFFFFFFu << (8 * head);
     const int r = total - 4 * (nw - 1);                        // 1..4 bytes in the last word
     const uint32_t mlast = r < 4 ? (1u << (8 * r)) - 1u : 0xFFFFFFFFu;
-    uint32_t acc;
+    uint32_t acc = 0;
+    // a word of plain ACGT/acgt is accepted by the cheap test; any other word (N, '.', or an
+    // invalid byte: 2.5 % of the warp's trips on the bench workloads) gets the exact one
+#define BSTR_CHECK_WORD(W_)                                                         \
+    { const uint32_t w_ = (W_); if (swar_not_acgt(w_)) acc |= swar_invalid(w_); }
     if (nw == 1) {
         const uint32_t m = mfirst & mlast;
-        acc = swar_invalid((wp[0] & m) | (0x41414141u & ~m));
+        BSTR_CHECK_WORD((wp[0] & m) | (0x41414141u & ~m))
     } else {
-        acc = swar_invalid((wp[0] & mfirst) | (0x41414141u & ~mfirst));
-        for (int i = 1; i < nw - 1; i++) acc |= swar_invalid(wp[i]);
-        acc |= swar_invalid((wp[nw - 1] & mlast) | (0x41414141u & ~mlast));
+        BSTR_CHECK_WORD((wp[0] & mfirst) | (0x41414141u & ~mfirst))
+        for (int i = 1; i < nw - 1; i++) BSTR_CHECK_WORD(wp[i])
+        BSTR_CHECK_WORD((wp[nw - 1] & mlast) | (0x41414141u & ~mlast))
     }
+#undef BSTR_CHECK_WORD
     return (acc & 0x01010101u) != 0;
 }
 

@@ -189,6 +189,9 @@ static TileGeom geometry_for_tile(const bstr_ctx *ctx, double rec_bytes, uint32_
     if (tile > fit && !ctx->geom_tile) { tile = (uint32_t)fit & ~15u; if (tile < FT_MINTILE) tile = FT_MINTILE; }
     uint32_t stage = ctx->geom_stage;
     if (!stage) stage = (uint32_t)(tile * (1.0 + 48.0 / rec_bytes) + rec_bytes) + 2048;
+    // phase D parks the matcher's per-warp work lists in the staging buffer (fused.cuh: WarpWork)
+    const uint32_t lists = (threads / 32) * 4u * warp_work_words<8>();
+    if (stage < lists && !ctx->geom_stage) stage = lists;
     stage = (stage + 15) & ~15u;
     TileGeom g = make_geometry(tile, threads, stage);
     if (g.smem_bytes > (uint32_t)FT_MAXSMEM)       // tiny records: a smaller stage, overflow -> generic kernels
