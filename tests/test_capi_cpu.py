@@ -67,6 +67,13 @@ def test_cli_contract_without_gpu():
     """Exit codes / streams of /root/reference/src/select_STR_reads:75-78,93-95,124-132."""
     r = _cli("-h")
     assert r.returncode == 0 and "usage:" in r.stderr and r.stdout == ""
+    # the usage text is the reference's, byte for byte (/root/reference/src/select_STR_reads:2-46, version filled in)
+    import hashlib
+    assert hashlib.md5(r.stderr.encode()).hexdigest() == "27021ebfa48636253a26e216e44e9f19"
+    if os.path.exists("/root/reference/src/select_STR_reads"):
+        ref = open("/root/reference/src/select_STR_reads").read()
+        a = ref.index('"""') + 3
+        assert r.stderr == ref[a:ref.index('"""', a)] % {"scriptVersion": "0.3.1"} + "\n"
     r = _cli("-v")
     assert r.returncode == 0 and r.stderr.splitlines()[0] == "Program: select_STR_reads"
     assert r.stderr.splitlines()[1] == "Version: 0.3.1"
