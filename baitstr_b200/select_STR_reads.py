@@ -49,39 +49,54 @@ def select_str_reads(filenames, num_minimum_copies, flanking_distance, illumina_
         sys.stderr.flush()
 
 
-def _run_files_reported(ctx, filenames, to_check, debug_flag):
-    """``-c`` and/or ``-d``: the GPU pipeline writes each file's annotated FASTQ to a temporary
-    file, which is copied to stdout unchanged; then the file's stderr reports follow in the
-    reference's order with one worker: per read its -d block (debug_report.py) and, if it was
-    selected, its -c "No match" line (check_strs.py); then "Done processing" (pyx:370)."""
+REPORT_BATCH_READS = 20000            # records per GPU batch of a -c / -d run: bounds the memory of the reports
+
+
+def _run_files_reported(ctx, filenames, to_check, debug_flag, batch_reads=None):
+    """``-c`` and/or ``-d``, streamed: the file is read `batch_reads` records at a time; every
+    batch goes through the GPU pipeline (bstr_scan_batch), its annotated FASTQ is written to
+    stdout unchanged, then its stderr reports follow in the reference's order with one worker:
+    per read its -d block (debug_report.py, enumerated on the GPU by bstr_debug_reads) and, if it
+    was selected, its -c "No match" line (check_strs.py, from the batch's own output); after the
+    last batch "Done processing" (pyx:370).  Memory is bounded by the batch, whatever the file size."""
+    import gzip
     import os
-    import tempfile
+    from itertools import islice
+    batch_reads = batch_reads or int(os.environ.get("BSTR_REPORT_BATCH_READS", "0")) or REPORT_BATCH_READS
     for fn in filenames:
-        with tempfile.TemporaryFile() as out, tempfile.TemporaryFile() as err:
-            failure = None
-            try:
-                ctx.run_files([fn], out_fd=out.fileno(), err_fd=err.fileno())
-            except Exception as e:                                      # noqa: BLE001 -- re-raised below
-                failure = e
-            out.seek(0)
-            data = out.read()
-            os.write(1, data)                 # everything before a bad record is still printed
-            check_lines = iter(check_strs_mod.annotated_fastq_lines(data, to_check)) if to_check is not None else None
-            if debug_flag and failure is None:
-                # a selected read's "No match" line follows its own block (both come out of the
-                # same ProcessSequence call, pyx:296-317)
-                for block, selected in debug_report.file_blocks(ctx, fn):
-                    sys.stderr.write(block)
-                    if selected and check_lines is not None:
-                        sys.stderr.write(next(check_lines, ""))
-            if check_lines is not None:
-                for line in check_lines:
-                    sys.stderr.write(line)
-            sys.stderr.flush()
-            err.seek(0)
-            os.write(2, err.read())
-            if failure is not None:
-                raise failure
+        opener = gzip.open if fn[-3:] == ".gz" else open                          # fastq.pyx:50-51
+        with opener(fn, "rb") as fh:
+            ahead = fh.readline()
+            rec_base = 0
+            while ahead:
+                lines = [ahead] + list(islice(fh, 4 * batch_reads - 1))
+                ahead = fh.readline()
+                raw = b"".join(lines)
+                try:
+                    out, info = ctx.scan_batch(raw, final=not ahead)
+                except capi.BstrError as e:
+                    if e.bad_record >= 0:
+                        raise capi.BstrError(e.code, "%s: record %d: %s" % (fn, rec_base + e.bad_record, ctx._lib.bstr_last_error(ctx._ctx).decode("latin-1", "replace")), rec_base + e.bad_record)
+                    raise
+                os.write(1, out)
+                check_lines = iter(check_strs_mod.annotated_fastq_lines(out, to_check)) if to_check is not None else None
+                if debug_flag:
+                    # a selected read's "No match" line follows its own block (both come out of the
+                    # same ProcessSequence call, pyx:296-317); names and bases as fastq.pyx:78,83
+                    nrec = int(info["n_records"])
+                    names = [l[1:-1].decode("latin-1") for l in lines[0:4 * nrec:4]]
+                    seqs = [l[:-1].upper() for l in lines[1:4 * nrec:4]]
+                    for name, (dinfo, fwd, rc) in zip(names, ctx.debug_reads(seqs)):
+                        sys.stderr.write(debug_report.render_read(name, dinfo, fwd, rc))
+                        if check_lines is not None and not (dinfo[1] or dinfo[5]):
+                            sys.stderr.write(next(check_lines, ""))
+                if check_lines is not None:
+                    for line in check_lines:
+                        sys.stderr.write(line)
+                sys.stderr.flush()
+                rec_base += int(info["n_records"])
+        sys.stderr.write("Done processing %s\n" % fn)                           # pyx:370
+        sys.stderr.flush()
 
 
 def _periods_and_copies(patterns):

@@ -40,10 +40,17 @@ def gzwrite(path, data):
 
 
 def fuzz_cases(ref):
-    rng = random.Random(0xBA175712)
+    return fuzz_block(ref, 0xBA175712, 6000, [2, 2, 2, 3, 3, 5], [0, 0, 3, 5, 8, 31, 31, 41]) + \
+        fuzz_block(ref, 0xBA175713, 3000, [0, 1, 1, 2, 3, 5], [0, 1, 5, 6, 7, 8, 31, 41])
+    # second block (round 2): the n <= 1 branch (every position is a one-copy match) and the
+    # window-origin boundary f = 6 / 7 (g0 = f - 6 in csrc/matcher.cuh) pinned to the reference too
+
+
+def fuzz_block(ref, seed, count, n_choices, f_choices):
+    rng = random.Random(seed)
     cases = []
     alphabets = ["ACGT", "ACGT", "AC", "ACGTN", "ACGT.", "ACGTN."]
-    for i in range(6000):
+    for i in range(count):
         alpha = alphabets[i % len(alphabets)]
         L = rng.choice([0, 1, 5, 13, 31, 32, 33, 63, 64, 65, 100, 100, 100, 150, 250])
         s = [rng.choice(alpha) for _ in range(L)]
@@ -56,8 +63,8 @@ def fuzz_cases(ref):
                 if pos + j < L:
                     s[pos + j] = motif[j % k]
         s = "".join(s)
-        n = rng.choice([2, 2, 2, 3, 3, 5])
-        f = rng.choice([0, 0, 3, 5, 8, 31, 31, 41])
+        n = rng.choice(n_choices)
+        f = rng.choice(f_choices)
         ks = rng.choice([[2, 3, 4, 5, 6]] * 3 + [[2], [3], [2, 3], [4], [5, 6], [6], [2, 4, 6]])
         rmhm = rng.random() < 0.3
         alt = rng.random() < 0.75

@@ -49,15 +49,3 @@ def test_blocks_match_reference_stderr(ci, tmp_path):
     if to_check is not None:
         check_strs.print_performance_log(to_check, err)
     assert err.getvalue() == case["stderr"]
-
-
-def test_reader_for_the_report(tmp_path):
-    """debug_report.read_names_and_bases: names without '@', bases upper-cased, .gz by suffix."""
-    raw = b"@r1 x\ty\nacgtn.\n+r1\nIIIIII\n@r2\n\n+\n\n"
-    p = tmp_path / "a.fq"
-    p.write_bytes(raw)
-    g = tmp_path / "a.fq.gz"
-    g.write_bytes(gzip.compress(raw))
-    want = [("r1 x\ty", b"ACGTN."), ("r2", b"")]
-    assert list(debug_report.read_names_and_bases(str(p))) == want
-    assert list(debug_report.read_names_and_bases(str(g))) == want

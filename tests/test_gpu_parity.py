@@ -285,6 +285,38 @@ def test_cli_debug_report(capi, tmp_path):
         assert len(out) == 3 and int(out[1][0][1]) == 1
 
 
+def test_cli_reports_are_streamed(capi, tmp_path):
+    """-c / -d runs go through the GPU a bounded batch of records at a time
+    (baitstr_b200/select_STR_reads.py: _run_files_reported): whatever the batch size -- one record,
+    a few, more than the file -- stdout and stderr are the same bytes, for plain and .gz input,
+    with and without a final newline."""
+    import gzip
+    raw = util.synth_fastq(700, 60, seed=77, p_str=0.6)[:-1]                 # unterminated last line
+    fq, gz, chk = str(tmp_path / "r.fq"), str(tmp_path / "r.fq.gz"), str(tmp_path / "check.txt")
+    open(fq, "wb").write(raw)
+    open(gz, "wb").write(gzip.compress(raw))
+    open(chk, "w").write("AC 3 ACGTACGTAC TTTTTGGGGG\n")
+    cli = os.path.join(util.ROOT, "bin", "select_STR_reads")
+    want = oracle.select_buffer(raw, f=5)
+    seen = set()
+    for path in (fq, gz):
+        for batch in ("1", "7", "256", "100000"):
+            r = subprocess.run([sys.executable, cli, "-f", "5", "-d", "-c", chk, path], capture_output=True,
+                               env=dict(os.environ, BSTR_REPORT_BATCH_READS=batch))
+            assert r.returncode == 0, r.stderr[-2000:]
+            assert r.stdout == want
+            seen.add(r.stderr.replace(path.encode(), b"FILE"))
+    assert len(seen) == 1 and b"Done processing FILE" in next(iter(seen))
+    # a bad record in a later batch: the batches before it are on stdout, the error names the record
+    lines = raw.split(b"\n")
+    lines[4 * 500 + 2] = b"-"
+    open(fq, "wb").write(b"\n".join(lines))
+    r = subprocess.run([sys.executable, cli, "-f", "5", "-d", fq], capture_output=True,
+                       env=dict(os.environ, BSTR_REPORT_BATCH_READS="64"))
+    assert r.returncode == 1 and b"record 500" in r.stderr
+    assert want.startswith(r.stdout) and len(r.stdout) > 0
+
+
 def test_full_size_properties(capi):
     """BASELINE-sized batches (1M x 100 bp, 0.5M x 150 bp): every selected record is the
     input record with an annotated header (round trip), order is preserved, counts agree
