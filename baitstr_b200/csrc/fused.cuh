@@ -221,11 +221,20 @@ template <int MODE> __device__ __forceinline__ uint8_t xform_byte(uint8_t c)
     return c;
 }
 
-// copy n bytes s -> d (both shared memory, any alignment) with aligned 32-bit stores
+// copy n bytes s -> d (both shared memory, any alignment) with aligned 32-bit stores.  No byte
+// loops: the up to three bytes in front of the first aligned word, the up to three words after
+// the last 16-byte trip and the up to three bytes at the end are predicated single operations,
+// so the lanes of a warp (different alignments) do not wait for each other's loop trips.
 template <int MODE>
 __device__ __forceinline__ uint8_t *copy_xform(uint8_t *d, const uint8_t *s, int n)
 {
-    while (n > 0 && ((uintptr_t)d & 3)) { *d++ = xform_byte<MODE>(*s++); n--; }
+    if (n <= 0) return d;
+    int k0 = (int)((4u - ((uint32_t)(uintptr_t)d & 3u)) & 3u);
+    if (k0 > n) k0 = n;
+    if (k0 > 0) d[0] = xform_byte<MODE>(s[0]);
+    if (k0 > 1) d[1] = xform_byte<MODE>(s[1]);
+    if (k0 > 2) d[2] = xform_byte<MODE>(s[2]);
+    d += k0; s += k0; n -= k0;
     const int nw = n >> 2;
     if (nw > 0) {
         const uint32_t *sp = (const uint32_t *)(s - ((uintptr_t)s & 3));   // keeps s's address space (LDS, not LD)
@@ -241,15 +250,40 @@ __device__ __forceinline__ uint8_t *copy_xform(uint8_t *d, const uint8_t *s, int
             dp[i + 3] = xform_word<MODE>(__funnelshift_r(w3, w4, sh));
             lo = w4;
         }
-        for (; i < nw; i++) {
-            const uint32_t hi = sp[i + 1];
-            dp[i] = xform_word<MODE>(__funnelshift_r(lo, hi, sh));
-            lo = hi;
+        const int rw = nw - i;                              // 0..3 words left
+        if (rw > 0) {
+            const uint32_t w1 = sp[i + 1];
+            dp[i] = xform_word<MODE>(__funnelshift_r(lo, w1, sh));
+            if (rw > 1) {
+                const uint32_t w2 = sp[i + 2];
+                dp[i + 1] = xform_word<MODE>(__funnelshift_r(w1, w2, sh));
+                if (rw > 2) dp[i + 2] = xform_word<MODE>(__funnelshift_r(w2, sp[i + 3], sh));
+            }
         }
         d += 4 * nw; s += 4 * nw; n -= 4 * nw;
     }
-    while (n > 0) { *d++ = xform_byte<MODE>(*s++); n--; }
-    return d;
+    if (n > 0) d[0] = xform_byte<MODE>(s[0]);
+    if (n > 1) d[1] = xform_byte<MODE>(s[1]);
+    if (n > 2) d[2] = xform_byte<MODE>(s[2]);
+    return d + n;
+}
+
+// decimal of v < 1000 at p, no branches: three characters are stored, the first being the leading
+// digit; the one or two characters behind a shorter number are overwritten by what follows
+__device__ __forceinline__ uint8_t *put_dec3(uint8_t *p, uint32_t v)
+{
+    const uint32_t h = v / 100u, r = v - 100u * h, t = r / 10u, u = r - 10u * t;
+    const bool g100 = v >= 100u, g10 = v >= 10u;
+    p[0] = (uint8_t)('0' + (g100 ? h : (g10 ? t : u)));
+    p[1] = (uint8_t)('0' + (g100 ? t : u));
+    p[2] = (uint8_t)('0' + u);
+    return p + 1 + (g10 ? 1 : 0) + (g100 ? 1 : 0);
+}
+__device__ __forceinline__ uint8_t upper_bf(uint8_t c) { return (uint8_t)(c & ~((c & 0x40) >> 1)); }      // letters only lose bit 5
+__device__ __forceinline__ uint8_t comp_upper_bf(uint8_t c)
+{   // A <-> T (xor 0x15), C <-> G (xor 0x04), N and '.' (bit 3) unchanged -- select_STR_reads.pyx:187-189 on upper case
+    const uint8_t x = (c & 8) ? 0 : ((c & 2) ? 0x04 : 0x15);
+    return (uint8_t)(c ^ x);
 }
 
 __device__ __forceinline__ void format_record_words(const uint8_t *in, const RecordLines &ln,
@@ -258,6 +292,29 @@ __device__ __forceinline__ void format_record_words(const uint8_t *in, const Rec
     const int L = (int)(ln.e1 - ln.s1);
     const int fk = rr.fck & 7, fc = rr.fck >> 3, rk = rr.rck & 7, rcn = rr.rck >> 3;
     p = copy_xform<XF_NONE>(p, in + ln.s0, (int)(ln.e0 - ln.s0));          // '@' + name (validated)
+    if (L < 1000) {
+        // Annotation without data-dependent branches: six motif characters and three digits are
+        // always stored and the pointer advances by the true width; the surplus is overwritten by
+        // the field that follows (the last one by '\n' and the bases, L >= 4 for a selected read).
+        // The surplus reads stay inside the staged window (16 bytes of slack on both sides).
+        *p = '\t';
+        const uint8_t *fm = in + ln.s1 + rr.fstart;
+#pragma unroll
+        for (int j = 0; j < 6; j++) p[1 + j] = upper_bf(fm[j]);
+        p += 1 + fk;
+        *p++ = '\t'; p = put_dec3(p, fc);
+        *p++ = '\t'; p = put_dec3(p, rr.fstart);
+        *p++ = '\t'; p = put_dec3(p, rr.fstart + fk * fc);
+        *p = '\t';
+        const uint8_t *rm = in + ln.s1 + (L - 1 - (int)rr.rstart);
+#pragma unroll
+        for (int j = 0; j < 6; j++) p[1 + j] = comp_upper_bf(upper_bf(rm[-j]));
+        p += 1 + rk;
+        *p++ = '\t'; p = put_dec3(p, rcn);
+        *p++ = '\t'; p = put_dec3(p, rr.rstart);
+        *p++ = '\t'; p = put_dec3(p, rr.rstart + rk * rcn);
+        *p++ = '\n';
+    } else {
     *p++ = '\t';
     for (int j = 0; j < fk; j++) *p++ = upper(in[ln.s1 + rr.fstart + j]);
     *p++ = '\t'; p = put_dec(p, fc);
@@ -269,6 +326,7 @@ __device__ __forceinline__ void format_record_words(const uint8_t *in, const Rec
     *p++ = '\t'; p = put_dec(p, rr.rstart);
     *p++ = '\t'; p = put_dec(p, rr.rstart + rk * rcn);
     *p++ = '\n';
+    }
     p = copy_xform<XF_UPPER>(p, in + ln.s1, L);
     *p++ = '\n'; *p++ = '+'; *p++ = '\n';
     const int Q = (int)(ln.e3 - ln.s3);
@@ -427,12 +485,20 @@ template <int WMAX> __host__ __device__ constexpr uint32_t warp_work_words() { r
 
 // Dispatch on the window width as match_read (matcher.cuh), with the warp work list.  `wmax` is
 // warp-uniform; reads wider than the compiled windows take the exact byte path inline.
+#ifndef BSTR_WORKLIST_MAXW
+#define BSTR_WORKLIST_MAXW 4       // widest window whose continuing pairs go through the warp work list (A/B builds: 0, 2)
+#endif
 template <int WMAX>
 __device__ __forceinline__ void match_read_tile(const uint8_t *seq, int L, const ScanParams &prm, int wmax,
                                                 uint32_t *work, Hit &fwd, Hit &rc)
 {
-    if (wmax <= 2) match_read_warp<2>(seq, L, prm, work, fwd, rc);
-    else if (WMAX >= 4 && wmax <= 4) match_read_warp<(WMAX >= 4 ? 4 : 2)>(seq, L, prm, work, fwd, rc);
+    if (wmax <= 2) {
+        if (BSTR_WORKLIST_MAXW >= 2) match_read_warp<2>(seq, L, prm, work, fwd, rc);
+        else match_read_bits<2>(seq, L, prm, fwd, rc);
+    } else if (WMAX >= 4 && wmax <= 4) {
+        if (BSTR_WORKLIST_MAXW >= 4) match_read_warp<(WMAX >= 4 ? 4 : 2)>(seq, L, prm, work, fwd, rc);
+        else match_read_bits<(WMAX >= 4 ? 4 : 2)>(seq, L, prm, fwd, rc);
+    }
     // 6- and 8-word windows keep the continuing pairs inline: with the scan state of such a window
     // live across the list run the kernel spills (180 / 504 bytes at the 168-register cap)
     else if (WMAX == 6 && wmax <= 6) match_read_bits<(WMAX == 6 ? 6 : 2)>(seq, L, prm, fwd, rc);
