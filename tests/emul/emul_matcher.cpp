@@ -12,6 +12,7 @@
 #define __device__
 #define __host__
 #define __forceinline__ inline __attribute__((always_inline))
+#define __noinline__ inline
 
 static inline uint32_t __funnelshift_r(uint32_t lo, uint32_t hi, uint32_t s)
 {
