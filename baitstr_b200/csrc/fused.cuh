@@ -334,58 +334,41 @@ __device__ __forceinline__ void format_record_words(const uint8_t *in, const Rec
     *p++ = '\n';
 }
 
-// Line index of this thread's chunks: packs the 16-bit newline masks of up to FT_MAXCPT chunks,
-// two per word, into mk[] and returns (newlines in the window) << 16 | (newlines in the owned
-// tile).  The common case -- every chunk of the thread inside the staged window and inside the
-// batch -- has no per-chunk tests at all.
-__device__ __forceinline__ uint32_t index_chunks_fast(const uint8_t *sin, const TileGeom &g, uint32_t c0, uint32_t (&mk)[FT_MAXCPT / 2])
+// Line index of this thread's chunks: packs the 16-bit newline masks of up to FT_MAXCPT
+// chunks into mk[] and returns (newlines in the window) << 16 | (newlines in the owned tile).
+// CAREFUL = the window reaches the end of the batch: bytes past n are masked and, on the
+// final batch, an unterminated last line gets its virtual newline.
+template <bool CAREFUL>
+__device__ __forceinline__ uint32_t index_chunks(const uint8_t *sin, const TileGeom &g, uint32_t c0,
+                                                 uint64_t ts, uint64_t n, int final, uint64_t (&mk)[FT_MAXCPT / 4])
 {
+    uint32_t cnt = 0;
+    const uint32_t own = g.tile / 16;
 #pragma unroll
     for (int i = 0; i < FT_MAXCPT; i++) {
         if (i < (int)g.cpt) {
-            const uint32_t m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * (c0 + i)));
-            mk[i >> 1] |= m << (16 * (i & 1));
+            const uint32_t c = c0 + i;
+            uint32_t m = 0;
+            if (c < g.chunks) {
+                if (!CAREFUL) {
+                    m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
+                } else {
+                    const uint64_t gpos = ts + 16ull * c;
+                    if (gpos < n) {
+                        m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
+                        const uint64_t rem = n - gpos;
+                        if (rem < 16) m &= (1u << rem) - 1u;
+                        // an unterminated last line: its last byte is dropped by line[:-1]
+                        // (fastq.pyx:78,83,90), i.e. it plays the newline
+                        if (final && rem <= 16) m |= 1u << (rem - 1);
+                    }
+                }
+            }
+            mk[i >> 2] |= (uint64_t)m << (16 * (i & 3));
+            const uint32_t pc = __popc(m);
+            cnt += (pc << 16) | (c < own ? pc : 0u);
         }
     }
-    uint32_t all = 0;
-#pragma unroll
-    for (int w = 0; w < FT_MAXCPT / 2; w++) all += __popc(mk[w]);
-    return all;
-}
-
-// The careful variant: chunks past the window or past the end of the batch, and -- on the final
-// batch -- the virtual newline of an unterminated last line.  A few threads per batch run it.
-__device__ __noinline__ uint32_t index_chunks_careful(const uint8_t *sin, uint32_t chunks, uint32_t cpt, uint32_t c0,
-                                                      uint64_t ts, uint64_t n, int final, uint32_t *mk)
-{
-    uint32_t all = 0;
-    for (uint32_t i = 0; i < cpt; i++) {
-        const uint32_t c = c0 + i;
-        uint32_t m = 0;
-        const uint64_t gpos = ts + 16ull * c;
-        if (c < chunks && gpos < n) {
-            m = nl_mask_of(*reinterpret_cast<const uint4 *>(sin + 16 * c));
-            const uint64_t rem = n - gpos;
-            if (rem < 16) m &= (1u << rem) - 1u;
-            // an unterminated last line: its last byte is dropped by line[:-1]
-            // (fastq.pyx:78,83,90), i.e. it plays the newline
-            if (final && rem <= 16) m |= 1u << (rem - 1);
-        }
-        mk[i >> 1] |= m << (16 * (i & 1));
-        all += __popc(m);
-    }
-    return all;
-}
-
-// newlines of the thread's chunks that lie inside the owned tile (chunk index < own)
-__device__ __forceinline__ uint32_t own_newlines(const uint32_t (&mk)[FT_MAXCPT / 2], uint32_t c0, uint32_t cpt, uint32_t own, uint32_t all)
-{
-    if (c0 + cpt <= own) return all;
-    if (c0 >= own) return 0u;
-    uint32_t cnt = 0;                                   // the one thread that straddles the tile end
-#pragma unroll
-    for (int i = 0; i < FT_MAXCPT; i++)
-        if (c0 + i < own) cnt += __popc((mk[i >> 1] >> (16 * (i & 1))) & 0xFFFFu);
     return cnt;
 }
 
@@ -579,17 +562,10 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     __syncthreads();
 
     // ---- B: line index of the window -----------------------------------------------------
-    uint32_t mk[FT_MAXCPT / 2] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint64_t mk[FT_MAXCPT / 4] = {0, 0, 0, 0};
     const uint32_t c0 = tid * g.cpt;
-    uint32_t cnt_thr;
-    if (!reach && c0 + g.cpt <= g.chunks) cnt_thr = index_chunks_fast(sin, g, c0, mk);
-    else {
-        uint32_t tmp[FT_MAXCPT / 2] = {0, 0, 0, 0, 0, 0, 0, 0};      // the out-of-line call gets its own array, mk[] stays in registers
-        cnt_thr = index_chunks_careful(sin, g.chunks, g.cpt, c0, ts, n, final, tmp);
-#pragma unroll
-        for (int w = 0; w < FT_MAXCPT / 2; w++) mk[w] = tmp[w];
-    }
-    const uint32_t cnt = cnt_thr << 16 | own_newlines(mk, c0, g.cpt, g.tile / 16, cnt_thr);   // all << 16 | own
+    const uint32_t cnt = reach ? index_chunks<true>(sin, g, c0, ts, n, final, mk)
+                               : index_chunks<false>(sin, g, c0, ts, n, final, mk);   // all << 16 | own
     uint32_t tot;
     const uint32_t ex = block_excl_scan(cnt, S.warp_tmp, &tot);
     const uint32_t shift = tile == 0 ? 1u : 0u;      // tile 0: virtual newline before byte 0
@@ -600,11 +576,11 @@ k_fused_tile(const uint8_t *__restrict__ in, uint64_t n, int final, ScanParams p
     {
         uint32_t idx = (ex >> 16) + shift;
 #pragma unroll
-        for (int w = 0; w < FT_MAXCPT / 2; w++) {
-            uint32_t m = mk[w];
-            const uint32_t base = 16u * (c0 + 2 * w) + 1u;
+        for (int w = 0; w < FT_MAXCPT / 4; w++) {
+            uint64_t m = mk[w];
+            const uint32_t base = 16u * (c0 + 4 * w) + 1u;
             while (m) {
-                const int b = __ffs((int)m) - 1;
+                const int b = __ffsll((long long)m) - 1;
                 m &= m - 1;
                 if (idx < g.nlmax) s_nl[idx] = (uint16_t)(base + b);
                 idx++;

@@ -601,7 +601,7 @@ __device__ __forceinline__ uint8_t strand_char(const uint8_t *seq, int L, bool r
     return c;
 }
 
-__device__ __noinline__ Hit match_strand_bytes(const uint8_t *seq, int L, bool rc, const ScanParams &prm,
+__device__ inline Hit match_strand_bytes(const uint8_t *seq, int L, bool rc, const ScanParams &prm,
                                          Hit *pre = nullptr /* -x: the winner before its flank / -r tests */)
 {
     const int n = prm.n < 1 ? 1 : prm.n;
