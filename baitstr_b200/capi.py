@@ -10,6 +10,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ABI_VERSION = 2
+NOALLOC_MAX_BYTES = 4 << 20           # BSTR_NOALLOC_MAX_BYTES
 
 
 def library_path():
@@ -56,7 +57,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
-           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe"]
+           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc"]
 
 _lib = None
 
@@ -87,6 +88,9 @@ def load_library():
     lib.bstr_run_files.restype = C.c_int
     lib.bstr_scan_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(BatchOut)]
     lib.bstr_scan_batch.restype = C.c_int
+    lib.bstr_scan_batch_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_uint64,
+                                            C.POINTER(BatchOut)]
+    lib.bstr_scan_batch_noalloc.restype = C.c_int
     lib.bstr_lanes.argtypes = [C.c_void_p]
     lib.bstr_lanes.restype = C.c_int
     lib.bstr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_int]
@@ -239,6 +243,22 @@ class Context:
             else:
                 info["results"] = np.zeros((0, 4), dtype=np.uint32)
         return out, info
+
+    def scan_batch_noalloc(self, raw, final=True, out_capacity=None):
+        """bstr_scan_batch_noalloc: as scan_batch, but the library allocates nothing (static device
+        scratch; raw at most NOALLOC_MAX_BYTES).  The output lands in a caller-owned numpy buffer."""
+        addr, n, keep = self._addr(raw)
+        cap = int(2 * n + 4096 if out_capacity is None else out_capacity)
+        out = np.empty(max(cap, 1), dtype=np.uint8)
+        bo = BatchOut()
+        rc = self._lib.bstr_scan_batch_noalloc(self._ctx, addr, n, int(bool(final)), out.ctypes.data, cap, C.byref(bo))
+        info = {"consumed": bo.consumed, "n_records": bo.n_records, "n_selected": bo.n_selected,
+                "out_bytes": bo.out_bytes}
+        if rc:
+            err = BstrError(rc, self._lib.bstr_last_error(self._ctx).decode("latin-1", "replace"), bo.bad_record)
+            err.info = info
+            raise err
+        return out[:bo.out_bytes].tobytes(), info
 
     def scan_batch_nocopy(self, raw, final=True, nbytes=None):
         """Like scan_batch but leaves the output in the library's pinned buffer (bench)."""

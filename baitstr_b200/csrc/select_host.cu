@@ -417,3 +417,4 @@ void bstr_host_free(void *p) { if (p) cudaFreeHost(p); }
 }  // extern "C"
 
 #include "batch_api.inc"
+#include "noalloc_api.inc"

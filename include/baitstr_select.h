@@ -168,6 +168,30 @@ int bstr_bench_resident(bstr_ctx *ctx, const uint8_t *const *raws, const uint64_
 int bstr_pcie_probe(bstr_ctx *ctx, const uint8_t *const *raws, const uint64_t *nbytes,
                     const uint64_t *out_bytes, int njobs, int mode, int reps, double *ms);
 
+/* bstr_scan_batch for callers that may not allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  This entry point has no counterpart in
+ * the reference.  It does the work of
+ * bstr_scan_batch -- H2D copy, the fused tile kernel, D2H copy -- and calls no cudaMalloc, cudaFree,
+ * cudaHostAlloc or other allocating routine: every device byte it needs (input staging, output,
+ * look-back words, batch state) lives in ONE static device array of about 12.1 MiB inside the
+ * library, which every GPU that loads the library holds until the process exits.
+ *   raw, nbytes    host memory; nbytes <= BSTR_NOALLOC_MAX_BYTES, else BSTR_ERR_TOO_LARGE
+ *   out            caller's buffer (host or device) of out_capacity bytes; receives the annotated
+ *                  FASTQ.  If it is too small the call fails with BSTR_ERR_TOO_LARGE and
+ *                  info->out_bytes says how much is needed (never more than 2 x nbytes + 4096 here;
+ *                  beyond that: BSTR_ERR_TOO_LARGE as well)
+ *   info           counts as for bstr_scan_batch; info->out == out, info->results == NULL
+ * Inputs the fused kernel's tile geometry cannot hold (a record that runs more than 4 KiB past the
+ * end of the ~40 KiB tile it starts in, ...) are
+ * refused with BSTR_ERR_TOO_LARGE instead of being re-run through the generic kernels, which need
+ * allocated tables.  All calls on a device share the array and it keeps the previous call's
+ * contents; what must start at zero is cleared at the start of each call.  Calls that overlapped
+ * on the GPU would race on it: within a process the entry point serialises them with a lock held
+ * until the call's last synchronize (other processes have their own copy of the array). */
+#define BSTR_NOALLOC_MAX_BYTES (4u << 20)
+int bstr_scan_batch_noalloc(bstr_ctx *ctx, const uint8_t *raw, uint64_t nbytes, int final,
+                            uint8_t *out, uint64_t out_capacity, bstr_batch_out *info);
+
 /* Page-locked host memory for callers that want their batches DMA'd without a staging
  * copy (bench.py's end-to-end leg).  Plain malloc'd buffers work too, only slower. */
 void *bstr_host_alloc(size_t nbytes);
