@@ -324,27 +324,50 @@ struct SegmentSource {
     // next segment in file order: index, -1 after the last, -2 on error.  Thread-safe; may block.
     virtual long claim(uint64_t *off, size_t *len, bool *last) = 0;
     // produce it at dst; *have = bytes written (<= len), *newlines = '\n' among them
-    virtual bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) = 0;
+    virtual bool fill(long k, uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) = 0;
+    virtual int file_of(long) { return file0; }            // index (into the path list) of the file segment k belongs to
+    int file0 = 0;
     virtual bool fold(const pinflate::SegmentInfo &, bool) { return true; }   // called in segment order
     virtual void cancel() {}
     virtual const char *error() { return nullptr; }
     size_t seg_bytes = 0;
 };
 
+// A run of consecutive plain files as ONE stream of segments: segment numbers continue across the
+// file boundaries, so while the last segments of one shard file are still being read, other
+// threads already read the first segments of the next files -- several files are in flight at
+// once and the reader threads never drain at a file boundary.  (The reference opens one file
+// after the other, src/select_STR_reads.pyx:359; output order only needs the stitcher and the
+// writer to go in file order, not the readers.)
 struct PlainSource : SegmentSource {
-    int fd; uint64_t fsize, nseg; std::atomic<uint64_t> next{0};
-    PlainSource(int fd_, uint64_t fsize_, size_t S) : fd(fd_), fsize(fsize_), nseg((fsize_ + S - 1) / S) { seg_bytes = S; }
+    struct File { int fd; uint64_t size, seg0, nseg; };
+    std::vector<File> files;
+    uint64_t nseg = 0;
+    std::atomic<uint64_t> next{0};
+    PlainSource(int first_file, size_t S) { file0 = first_file; seg_bytes = S; }
+    void add(int fd, uint64_t size) { const uint64_t n = (size + seg_bytes - 1) / seg_bytes; files.push_back(File{fd, size, nseg, n}); nseg += n; }
+    const File &of(long k, int *idx = nullptr) const
+    {
+        size_t lo = 0, hi = files.size() - 1;
+        while (lo < hi) { const size_t mid = (lo + hi + 1) / 2; if (files[mid].seg0 <= (uint64_t)k) lo = mid; else hi = mid - 1; }
+        if (idx) *idx = (int)lo;
+        return files[lo];
+    }
+    int file_of(long k) override { int i; of(k, &i); return file0 + i; }
     long claim(uint64_t *off, size_t *len, bool *last) override
     {
         const uint64_t k = next.fetch_add(1);
         if (k >= nseg) return -1;
-        *off = k * seg_bytes;
-        *len = (size_t)(fsize - *off < seg_bytes ? fsize - *off : seg_bytes);
-        *last = k + 1 == nseg;
+        const File &f = of((long)k);
+        const uint64_t j = k - f.seg0;
+        *off = j * seg_bytes;
+        *len = (size_t)(f.size - *off < seg_bytes ? f.size - *off : seg_bytes);
+        *last = j + 1 == f.nseg;                          // last segment of ITS file
         return (long)k;
     }
-    bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *) override
+    bool fill(long k, uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *) override
     {
+        const int fd = of(k).fd;
         size_t got = 0;
         while (got < len) {
             ssize_t r = pread(fd, dst + got, len - got, (off_t)(off + got));
@@ -357,6 +380,7 @@ struct PlainSource : SegmentSource {
         *newlines = count_newlines(dst, got);
         return true;
     }
+    void close_all() { for (auto &f : files) if (f.fd >= 0) { close(f.fd); f.fd = -1; } }
 };
 
 struct GzipSource : SegmentSource {
@@ -372,7 +396,7 @@ struct GzipSource : SegmentSource {
         return z.open(map, size, threads, (size_t)1 << 20, S, pending);
     }
     long claim(uint64_t *off, size_t *len, bool *last) override { return z.claim(off, len, last); }
-    bool fill(uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) override
+    bool fill(long, uint64_t off, size_t len, uint8_t *dst, size_t *have, uint64_t *newlines, pinflate::SegmentInfo *info) override
     {
         if (!z.fill(off, len, dst, info)) return false;
         *have = len; *newlines = info->newlines;
@@ -385,13 +409,14 @@ struct GzipSource : SegmentSource {
 
 struct Segment {
     PinnedBuf buf;
+    int file;
     size_t len;
     uint64_t lines;
     bool failed, last;
     pinflate::SegmentInfo info;
 };
 
-static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int nthreads)
+static bool read_segments_parallel(Pipeline &P, SegmentSource &src, int nthreads)
 {
     const size_t HEAD = 1u << 20;
     std::map<long, Segment> segs;
@@ -401,7 +426,7 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
     std::vector<uint8_t> tail;
     bool stop = false;
 
-    auto fail = [&](PinnedBuf b, const char *what) {      // mu held
+    auto fail = [&](PinnedBuf b, const char *what, int fi) {      // mu held
         const char *detail = src.error();
         if (detail && *detail) errno = 0;
         reader_fail(P, fi, b, what, P.paths[fi], detail && *detail ? detail : nullptr);
@@ -415,8 +440,9 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
             Segment g = std::move(it->second);
             segs.erase(it);
             const bool lastseg = g.last;
-            if (g.failed) { fail(g.buf, "read error on"); break; }
-            if (!src.fold(g.info, lastseg)) { fail(g.buf, "read error on"); break; }
+            const int fi = g.file;
+            if (g.failed) { fail(g.buf, "read error on", fi); break; }
+            if (!src.fold(g.info, lastseg)) { fail(g.buf, "read error on", fi); break; }
             uint8_t *seg = g.buf.p + HEAD;
             const uint64_t total = lines + g.lines;
             size_t cut = 0;
@@ -440,7 +466,7 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
                     PinnedBuf big{nullptr, tail.size() + cut + 1};
                     if (big.cap > (2ull << 30) || cudaHostAlloc((void **)&big.p, big.cap, cudaHostAllocPortable) != cudaSuccess) {
                         cudaGetLastError(); errno = ENOMEM;
-                        fail(g.buf, "record too large reading"); break;
+                        fail(g.buf, "record too large reading", fi); break;
                     }
                     memcpy(big.p, tail.data(), tail.size());
                     memcpy(big.p + tail.size(), seg, cut);
@@ -450,7 +476,7 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
                 emit(P, j);
                 tail.swap(carry);
             }
-            lines = total;
+            lines = lastseg ? 0 : total;                 // the next segment starts the next file of the run
             frontier++;
         }
     };
@@ -461,7 +487,7 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
             PinnedBuf b = get_buf(P);                    // buffer first: the lowest unproduced segment always has one
             {
                 std::lock_guard<std::mutex> g(mu);
-                if (!b.p) { if (!P.abort_seen() && !stop) { errno = ENOMEM; fail(b, "out of page-locked memory reading"); } stop = true; src.cancel(); return; }
+                if (!b.p) { if (!P.abort_seen() && !stop) { errno = ENOMEM; fail(b, "out of page-locked memory reading", src.file_of(frontier)); } stop = true; src.cancel(); return; }
                 if (stop) { put_buf(P, b); return; }
             }
             uint64_t off = 0; size_t len = 0; bool last = false;
@@ -469,13 +495,13 @@ static bool read_segments_parallel(Pipeline &P, int fi, SegmentSource &src, int 
             if (k == -1) { put_buf(P, b); return; }
             if (k < 0) {
                 std::lock_guard<std::mutex> g(mu);
-                if (!stop && !P.abort_seen()) fail(b, "read error on"); else put_buf(P, b);
+                if (!stop && !P.abort_seen()) fail(b, "read error on", src.file_of(frontier)); else put_buf(P, b);
                 return;
             }
             Segment sg;
-            sg.buf = b; sg.len = 0; sg.lines = 0; sg.last = last;
+            sg.buf = b; sg.len = 0; sg.lines = 0; sg.last = last; sg.file = src.file_of(k);
             const double t0 = now_ms();
-            sg.failed = !src.fill(off, len, b.p + HEAD, &sg.len, &sg.lines, &sg.info);
+            sg.failed = !src.fill(k, off, len, b.p + HEAD, &sg.len, &sg.lines, &sg.info);
             const double t1 = now_ms();
             { std::lock_guard<std::mutex> g(P.mu); P.t_read += t1 - t0; }
             std::lock_guard<std::mutex> g(mu);
@@ -499,12 +525,32 @@ static void reader_main(Pipeline *pp)
         errno = 0;
         if (src.open_path(P.paths[fi]) != 0) { reader_fail(P, fi, PinnedBuf{nullptr, 0}, "cannot open", P.paths[fi]); break; }
         struct stat sb;
-        if (!src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && fstat(src.fd, &sb) == 0 && S_ISREG(sb.st_mode) &&
-            (uint64_t)sb.st_size > P.buf_cap) {
-            PlainSource ps(src.fd, (uint64_t)sb.st_size, P.buf_cap - (1u << 20));
-            const bool ok = read_segments_parallel(P, fi, ps, P.plain_readers);
+        auto big_plain = [&](int fd, struct stat *st) {
+            return P.n_readers > 1 && P.buf_cap >= (4u << 20) && fstat(fd, st) == 0 && S_ISREG(st->st_mode) && (uint64_t)st->st_size > P.buf_cap;
+        };
+        if (!src.is_gz && big_plain(src.fd, &sb)) {
+            // this file and the plain files that follow it in argv order (each larger than one batch)
+            // go through the parallel segment reader as ONE run, so their reads overlap
+            PlainSource ps(fi, P.buf_cap - (1u << 20));
+            ps.add(src.fd, (uint64_t)sb.st_size);
+            src.fd = -1;
+            int fj = fi + 1;
+            for (; fj < P.npaths && fj - fi < 64; fj++) {
+                const size_t n = strlen(P.paths[fj]);
+                if (n >= 3 && strcmp(P.paths[fj] + n - 3, ".gz") == 0) break;
+                const int fd = open(P.paths[fj], O_RDONLY);
+                struct stat sj;
+                if (fd < 0 || !big_plain(fd, &sj)) { if (fd >= 0) close(fd); break; }     // handled in its turn (errors stay in file order)
+#ifdef POSIX_FADV_SEQUENTIAL
+                posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
+                ps.add(fd, (uint64_t)sj.st_size);
+            }
+            const bool ok = read_segments_parallel(P, ps, P.plain_readers);
+            ps.close_all();
             src.close_all();
             if (!ok) break;
+            fi = fj - 1;
             continue;
         }
         if (src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && !getenv("BSTR_SERIAL_INFLATE")) {
@@ -515,7 +561,8 @@ static void reader_main(Pipeline *pp)
                 GzipSource gs;
                 const size_t S = P.buf_cap - (1u << 20) < ((size_t)32 << 20) ? P.buf_cap - (1u << 20) : (size_t)32 << 20;
                 if (gs.open(fd, (size_t)sb.st_size, P.gz_decoders, S, P.gz_pending)) {
-                    ok = read_segments_parallel(P, fi, gs, P.gz_fillers);
+                    gs.file0 = fi;
+                    ok = read_segments_parallel(P, gs, P.gz_fillers);
                     done = true;
                     if (getenv("BSTR_TRACE")) {
                         const pinflate::Stats zs = gs.z.stats();

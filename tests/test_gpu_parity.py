@@ -533,6 +533,53 @@ def test_run_files_parallel_segment_reader(capi, tmp_path):
         assert st["records"] == 60000 + 40001 and st["batches"] >= 6
 
 
+def test_run_files_runs_of_plain_files(capi, tmp_path):
+    """Consecutive plain files larger than a batch are read as ONE stream of segments, several
+    files in flight (stream_host.cu: PlainSource); the output is still every file's records in argv
+    order (select_STR_reads.pyx:359), "Done processing" lines included, whatever breaks a run: a
+    small file, a .gz file, an empty file.  A file that is missing is an error in ITS turn (what
+    precedes it is written), and a bad record names its own file and the record index in it."""
+    import gzip
+    raws = [util.synth_fastq(24000 + 3000 * i, 100 + 10 * (i % 2), seed=950 + i, tag="r%d" % i, p_str=0.5) for i in range(5)]
+    small = util.synth_fastq(50, 100, seed=960, tag="sm")
+    paths = []
+    for i, r in enumerate(raws):
+        pth = str(tmp_path / ("run%d.fq" % i))
+        open(pth, "wb").write(r if i != 2 else r[:-1])          # the third file lacks its final newline
+        paths.append(pth)
+    ps, pe, pg = str(tmp_path / "small.fq"), str(tmp_path / "empty.fq"), str(tmp_path / "z.fq.gz")
+    open(ps, "wb").write(small)
+    open(pe, "wb").write(b"")
+    open(pg, "wb").write(gzip.compress(raws[0], 1))
+    sel = [oracle.select_buffer(r) for r in raws]
+    sel[2] = oracle.select_buffer(raws[2][:-1])
+    order = [paths[0], paths[1], paths[2], ps, paths[3], pe, pg, paths[4], paths[0]]
+    want = sel[0] + sel[1] + sel[2] + oracle.select_buffer(small) + sel[3] + sel[0] + sel[4] + sel[0]
+    for threads in (0, 5):
+        outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+        with capi.Context(batch_bytes=4 << 20, host_threads=threads) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            ctx.run_files(order, out_fd=fo.fileno(), err_fd=fe.fileno())
+        assert open(outp, "rb").read() == want
+        assert open(errp).read() == "".join("Done processing %s\n" % q for q in order)
+    # a missing file after a run: the run's output is written, then the error
+    outp = str(tmp_path / "o2.fq")
+    with capi.Context(batch_bytes=4 << 20) as ctx, open(outp, "wb") as fo:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files([paths[0], paths[1], str(tmp_path / "nope.fq"), paths[3]], out_fd=fo.fileno(), err_fd=-1)
+        assert ei.value.code == -4 and "nope.fq" in str(ei.value)
+    assert open(outp, "rb").read() == sel[0] + sel[1]
+    # a bad record in the second file of a run
+    lines = raws[1].split(b"\n")
+    lines[4 * 20000 + 2] = b"-"
+    open(paths[1], "wb").write(b"\n".join(lines))
+    with capi.Context(batch_bytes=4 << 20) as ctx, open(outp, "wb") as fo:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files([paths[0], paths[1], paths[3]], out_fd=fo.fileno(), err_fd=-1)
+        assert ei.value.code == -12 and "run1.fq" in str(ei.value) and "record 20000" in str(ei.value)
+    got = open(outp, "rb").read()
+    assert got.startswith(sel[0]) and (sel[0] + sel[1]).startswith(got[:len(sel[0]) + 1000]) and len(got) < len(sel[0] + sel[1])
+
+
 def test_run_files_parallel_inflate(capi, tmp_path):
     """'*.gz' inputs of some size are inflated on several threads (pinflate.cpp) and fed to the GPU
     in segments stitched at record boundaries: same bytes as the oracle for a single-member file,
