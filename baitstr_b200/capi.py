@@ -57,7 +57,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
-           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc"]
+           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu"]
 
 _lib = None
 
@@ -122,6 +122,8 @@ def load_library():
     lib.bstr_device_count.restype = C.c_int
     lib.bstr_gunzip.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
     lib.bstr_gunzip.restype = C.c_int
+    lib.bstr_gunzip_gpu.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
+    lib.bstr_gunzip_gpu.restype = C.c_int
     _lib = lib
     return lib
 
@@ -137,6 +139,17 @@ def gunzip(path, out_fd=-1, threads=4, range_bytes=1 << 20, seg_bytes=8 << 20):
     st = (C.c_uint64 * 6)()
     err = C.create_string_buffer(512)
     rc = lib.bstr_gunzip(os.fsencode(path), out_fd, threads, range_bytes, seg_bytes, st, err, len(err))
+    if rc != 0:
+        raise BstrError(rc, err.value.decode("latin-1"))
+    return dict(zip(("in_bytes", "out_bytes", "ranges", "accepted", "redone", "members"), [int(x) for x in st]))
+
+
+def gunzip_gpu(path, out_fd=-1, device=0, window_bytes=0, range_bytes=0):
+    """bstr_gunzip_gpu: inflate `path` with the GPU inflater (csrc/ginflate.cu) on CUDA device `device`."""
+    lib = load_library()
+    st = (C.c_uint64 * 6)()
+    err = C.create_string_buffer(512)
+    rc = lib.bstr_gunzip_gpu(os.fsencode(path), out_fd, device, window_bytes, range_bytes, st, err, len(err))
     if rc != 0:
         raise BstrError(rc, err.value.decode("latin-1"))
     return dict(zip(("in_bytes", "out_bytes", "ranges", "accepted", "redone", "members"), [int(x) for x in st]))

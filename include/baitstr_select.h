@@ -221,6 +221,17 @@ int bstr_geometry_probe(double record_bytes, int window_words, uint32_t out[8]);
 int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes, uint64_t seg_bytes,
                 uint64_t *stats6, char *err, size_t errlen);
 
+/* The same for the GPU inflater (csrc/ginflate.cu), which bstr_run_files uses for "*.gz" inputs of
+ * some size: the compressed file is cut into windows of window_bytes (0: 64 MiB) and ranges of
+ * range_bytes (0: 64 KiB); one warp per range decodes DEFLATE into 16-bit symbols from a guessed
+ * block start, a chain check accepts the runs, the 32 KiB history is propagated, symbols become
+ * bytes and every member's CRC-32 / ISIZE is checked -- all on CUDA device `device`; only the
+ * inflated bytes this hook writes to out_fd (-1: discard) come back to the host.  Accepts and rejects
+ * the same files as bstr_gunzip / Python's gzip module (the reference reads through it,
+ * src/fastq.pyx:50-51).  stats6 as for bstr_gunzip.  Needs a CUDA device. */
+int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_t window_bytes, uint64_t range_bytes,
+                    uint64_t *stats6, char *err, size_t errlen);
+
 /* number of CUDA devices visible (0 if none / no driver) */
 int bstr_device_count(void);
 
