@@ -6,11 +6,33 @@
 #include <string.h>
 #include <zlib.h>                      // crc32_combine only
 
+#include <chrono>
 #include <vector>
 
 #include "ginflate_dev.cuh"
 
 namespace ginflate {
+
+// ---- CRC-32 of a concatenation from the CRCs of its parts (as zlib's crc32_combine): crc(A || B) =
+// crc(A) * x^(8 |B|) mod P  xor  crc(B) over GF(2), bit-reflected polynomial 0xEDB88320.  The operator
+// x^(8 n) mod P for the fixed chunk length is computed once.
+constexpr uint32_t CRC_CHUNK = 8u << 10;
+static uint32_t gf2_multmodp(uint32_t a, uint32_t b)
+{
+    uint32_t m = 1u << 31, p = 0;
+    for (;;) {
+        if (a & m) { p ^= b; if ((a & (m - 1)) == 0) break; }
+        m >>= 1;
+        b = b & 1 ? (b >> 1) ^ 0xEDB88320u : b >> 1;
+    }
+    return p;
+}
+static uint32_t gf2_x2n(uint64_t nbytes)           // x^(8 nbytes) mod P
+{
+    uint32_t p = 1u << 31, sq = 1u << 23;          // x^0, x^8
+    for (uint64_t n = nbytes; n; n >>= 1) { if (n & 1) p = gf2_multmodp(sq, p); sq = gf2_multmodp(sq, sq); }
+    return p;
+}
 
 struct DeviceImpl {
     size_t window_bytes = 0, look_ahead = 0, range_bytes = 0;
@@ -22,6 +44,7 @@ struct DeviceImpl {
     RangeDesc *d_desc = nullptr; RangeMeta *d_meta = nullptr;
     RunRef *d_runs = nullptr;    uint8_t *d_hist = nullptr;     // (max_ranges + 2) x 32 KiB
     CrcChunk *d_chunks = nullptr; uint32_t *d_crc = nullptr; size_t cap_chunks = 0;
+    WarpTables *d_tables = nullptr;                             // one slot per range (global memory, L1-resident while a warp decodes)
     // pinned host mirrors
     RangeDesc *h_desc = nullptr; RangeMeta *h_meta = nullptr; RunRef *h_runs = nullptr;
     CrcChunk *h_chunks = nullptr; uint32_t *h_crc = nullptr;
@@ -37,6 +60,8 @@ struct DeviceImpl {
     bool stream_end = false;
     char err[256] = {0};
     size_t dev_bytes = 0;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double ms_upload = 0, ms_decode = 0, ms_propagate = 0;      // CUDA-event times, summed over the windows (BSTR_TRACE)
 
     int fail(const char *fmt, ...)
     {
@@ -72,12 +97,24 @@ Device *Device::create(size_t window_bytes, size_t look_ahead, size_t range_byte
     if ((e = cudaMalloc((void **)&p->d_meta, nr * sizeof(RangeMeta))) != cudaSuccess) return bail("range table", e);
     if ((e = cudaMalloc((void **)&p->d_runs, nr * sizeof(RunRef))) != cudaSuccess) return bail("run table", e);
     if ((e = cudaMalloc((void **)&p->d_hist, nr * 32768)) != cudaSuccess) return bail("history", e);
+    if ((e = cudaMalloc((void **)&p->d_tables, nr * sizeof(WarpTables))) != cudaSuccess) return bail("Huffman tables", e);
     if ((e = cudaHostAlloc((void **)&p->h_desc, nr * sizeof(RangeDesc), cudaHostAllocPortable)) != cudaSuccess) return bail("pinned tables", e);
     if ((e = cudaHostAlloc((void **)&p->h_meta, nr * sizeof(RangeMeta), cudaHostAllocPortable)) != cudaSuccess) return bail("pinned tables", e);
     if ((e = cudaHostAlloc((void **)&p->h_runs, nr * sizeof(RunRef), cudaHostAllocPortable)) != cudaSuccess) return bail("pinned tables", e);
-    p->dev_bytes = p->cap_comp + p->cap_arena * 2 + nr * (sizeof(RangeDesc) + sizeof(RangeMeta) + sizeof(RunRef) + 32768);
-    e = cudaFuncSetAttribute(k_decode_ranges, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WARPS_PER_CTA * sizeof(WarpTables)));
-    if (e != cudaSuccess) return bail("shared memory of the decode kernel", e);
+    p->dev_bytes = p->cap_comp + p->cap_arena * 2 + nr * (sizeof(RangeDesc) + sizeof(RangeMeta) + sizeof(RunRef) + 32768 + sizeof(WarpTables));
+    e = cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+    if (e != cudaSuccess) return bail("shared memory of the propagate kernel", e);
+    cudaFuncSetAttribute(k_decode_ranges, cudaFuncAttributePreferredSharedMemoryCarveout, 0);     // all of the SM's L1 for the tables
+    for (int i = 0; i < 4; i++) cudaEventCreate(&p->ev[i]);
+    {
+        static uint16_t kraft4[4096];
+        for (int i = 0; i < 4096; i++) {
+            int k = 0;
+            for (int j = 0; j < 4; j++) { const int l = (i >> (3 * j)) & 7; k += l ? 128 >> l : 0; }
+            kraft4[i] = (uint16_t)k;
+        }
+        if ((e = cudaMemcpyToSymbol(g_kraft4, kraft4, sizeof(kraft4))) != cudaSuccess) return bail("search table", e);
+    }
     return d;
 }
 
@@ -85,24 +122,25 @@ Device::~Device()
 {
     if (!p) return;
     cudaFree(p->d_comp); cudaFree(p->d_arena); cudaFree(p->d_desc); cudaFree(p->d_meta); cudaFree(p->d_runs); cudaFree(p->d_hist);
-    cudaFree(p->d_chunks); cudaFree(p->d_crc);
+    cudaFree(p->d_chunks); cudaFree(p->d_crc); cudaFree(p->d_tables);
     if (p->h_desc) cudaFreeHost(p->h_desc);
     if (p->h_meta) cudaFreeHost(p->h_meta);
     if (p->h_runs) cudaFreeHost(p->h_runs);
     if (p->h_chunks) cudaFreeHost(p->h_chunks);
     if (p->h_crc) cudaFreeHost(p->h_crc);
+    for (int i = 0; i < 4; i++) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
     delete p;
 }
 
 const char *Device::error() const { return p->err; }
 uint64_t Device::text_bytes() const { return p->text; }
 size_t Device::device_bytes() const { return p->dev_bytes; }
+void Device::kernel_ms(double *upload, double *decode, double *propagate) const { *upload = p->ms_upload; *decode = p->ms_decode; *propagate = p->ms_propagate; }
 
 static int launch_decode(DeviceImpl *p, int n, cudaStream_t st)
 {
     const int ctas = (n + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
-    k_decode_ranges<<<ctas, 32 * WARPS_PER_CTA, WARPS_PER_CTA * sizeof(WarpTables), st>>>(p->d_comp, p->nbytes, p->at_eof ? 1 : 0, p->d_desc, n,
-                                                                                         p->d_arena, p->d_meta);
+    k_decode_ranges<<<ctas, 32 * WARPS_PER_CTA, 0, st>>>(p->d_comp, p->nbytes, p->at_eof ? 1 : 0, p->d_desc, n, p->d_arena, p->d_meta, p->d_tables);
     return p->cuda(cudaGetLastError(), "k_decode_ranges");
 }
 
@@ -111,6 +149,7 @@ int Device::decode(const uint8_t *comp, size_t nbytes, size_t own_bytes, uint64_
     if (nbytes + 64 > p->cap_comp || own_bytes > p->window_bytes || own_bytes > nbytes) return p->fail("GPU inflater: window larger than the working set");
     p->nbytes = nbytes; p->own_bytes = own_bytes; p->file_off = file_off; p->at_eof = at_eof;
     p->err[0] = 0;
+    cudaEventRecord(p->ev[0], st);
     GI_TRY(cudaMemcpyAsync(p->d_comp, comp, nbytes, cudaMemcpyHostToDevice, st));
     GI_TRY(cudaMemsetAsync(p->d_comp + nbytes, 0, 64, st));
     const size_t R = p->range_bytes;
@@ -124,9 +163,14 @@ int Device::decode(const uint8_t *comp, size_t nbytes, size_t own_bytes, uint64_
         d.mode = (r == 0 && file_off == 0) ? 2 : 0;
     }
     GI_TRY(cudaMemcpyAsync(p->d_desc, p->h_desc, (size_t)p->nranges * sizeof(RangeDesc), cudaMemcpyHostToDevice, st));
+    cudaEventRecord(p->ev[1], st);
     if (launch_decode(p, p->nranges, st)) return -1;
+    cudaEventRecord(p->ev[2], st);
     GI_TRY(cudaMemcpyAsync(p->h_meta, p->d_meta, (size_t)p->nranges * sizeof(RangeMeta), cudaMemcpyDeviceToHost, st));
     GI_TRY(cudaStreamSynchronize(st));
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, p->ev[0], p->ev[1]); cudaEventElapsedTime(&b, p->ev[1], p->ev[2]);
+    p->ms_upload += a; p->ms_decode += b;
     return 0;
 }
 
@@ -160,9 +204,8 @@ int Device::chain(FileState &fs, cudaStream_t st)
             RangeDesc x = d;
             x.from_bit = expected; x.mode = 1;
             GI_TRY(cudaMemcpyAsync(p->d_desc + p->max_ranges + 1, &x, sizeof(x), cudaMemcpyHostToDevice, st));
-            k_decode_ranges<<<1, 32 * WARPS_PER_CTA, WARPS_PER_CTA * sizeof(WarpTables), st>>>(p->d_comp, p->nbytes, p->at_eof ? 1 : 0,
-                                                                                             p->d_desc + p->max_ranges + 1, 1, p->d_arena,
-                                                                                             p->d_meta + p->max_ranges + 1);
+            k_decode_ranges<<<1, 32 * WARPS_PER_CTA, 0, st>>>(p->d_comp, p->nbytes, p->at_eof ? 1 : 0, p->d_desc + p->max_ranges + 1, 1, p->d_arena,
+                                                            p->d_meta + p->max_ranges + 1, p->d_tables + p->max_ranges + 1);
             GI_TRY(cudaGetLastError());
             GI_TRY(cudaMemcpyAsync(&redo, p->d_meta + p->max_ranges + 1, sizeof(RangeMeta), cudaMemcpyDeviceToHost, st));
             GI_TRY(cudaStreamSynchronize(st));
@@ -187,11 +230,14 @@ int Device::chain(FileState &fs, cudaStream_t st)
     GI_TRY(cudaMemcpyAsync(p->d_hist, fs.hist, 32768, cudaMemcpyHostToDevice, st));
     if (p->nruns) {
         GI_TRY(cudaMemcpyAsync(p->d_runs, p->h_runs, (size_t)p->nruns * sizeof(RunRef), cudaMemcpyHostToDevice, st));
-        k_propagate<<<1, 1024, 0, st>>>(p->d_arena, p->d_runs, p->nruns, p->d_hist);
+        cudaEventRecord(p->ev[0], st);
+        k_propagate<<<1, 1024, 65536, st>>>(p->d_arena, p->d_runs, p->nruns, p->d_hist);
         GI_TRY(cudaGetLastError());
+        cudaEventRecord(p->ev[3], st);
     }
     GI_TRY(cudaMemcpyAsync(fs.hist, p->d_hist + (size_t)p->nruns * 32768, 32768, cudaMemcpyDeviceToHost, st));
     GI_TRY(cudaStreamSynchronize(st));
+    if (p->nruns) { float a = 0; cudaEventElapsedTime(&a, p->ev[0], p->ev[3]); p->ms_propagate += a; }
     fs.out_bytes += p->text;
     return 0;
 }
@@ -199,7 +245,7 @@ int Device::chain(FileState &fs, cudaStream_t st)
 int Device::crc_launch(cudaStream_t st)
 {
     // pieces = the window's text cut at the member ends; chunks = pieces cut at run boundaries and every 128 KiB
-    const uint32_t CH = 128u << 10;
+    const uint32_t CH = CRC_CHUNK;
     std::vector<CrcChunk> chunks;
     p->pieces.clear();
     size_t e = 0;
@@ -248,10 +294,12 @@ int Device::crc_launch(cudaStream_t st)
 int Device::crc_fold(FileState &fs, cudaStream_t st)
 {
     GI_TRY(cudaStreamSynchronize(st));
+    static const uint32_t op_full = gf2_x2n(CRC_CHUNK);
     for (const DeviceImpl::Piece &pc : p->pieces) {
         for (uint32_t c = 0; c < pc.nchunks; c++) {
             const uint32_t n = p->h_chunks[pc.first_chunk + c].n;
-            fs.crc = fs.len == 0 ? p->h_crc[pc.first_chunk + c] : (uint32_t)crc32_combine(fs.crc, p->h_crc[pc.first_chunk + c], (z_off_t)n);
+            const uint32_t cc = p->h_crc[pc.first_chunk + c];
+            fs.crc = fs.len == 0 ? cc : gf2_multmodp(n == CRC_CHUNK ? op_full : gf2_x2n(n), fs.crc) ^ cc;
             fs.len += n;
         }
         if (pc.end >= 0) {
@@ -278,6 +326,7 @@ int Device::resolve(uint8_t *d_text, cudaStream_t st)
 // ---- host-only-interface test hook: inflate one .gz file on one GPU, bytes to out_fd -----------------
 #include <errno.h>
 #include <fcntl.h>
+#include <stdlib.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -298,8 +347,8 @@ extern "C" int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_
     void *map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
     close(fd);
     if (map == MAP_FAILED) { say(strerror(errno)); return BSTR_ERR_IO; }
-    const size_t W = window_bytes ? (size_t)window_bytes : (size_t)64 << 20, LA = (size_t)4 << 20;
-    ginflate::Device *dev = ginflate::Device::create(W, LA, range_bytes ? (size_t)range_bytes : (size_t)64 << 10, err, errlen);
+    const size_t W = window_bytes ? (size_t)window_bytes : ginflate::DEFAULT_WINDOW, LA = ginflate::LOOK_AHEAD;
+    ginflate::Device *dev = ginflate::Device::create(W, LA, range_bytes ? (size_t)range_bytes : ginflate::DEFAULT_RANGE, err, errlen);
     if (!dev) { munmap(map, size); return BSTR_ERR_CUDA; }
     cudaStream_t st = nullptr;
     cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
@@ -307,13 +356,22 @@ extern "C" int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_
     uint8_t *d_text = nullptr; size_t cap_text = 0;
     std::vector<uint8_t> host;
     int rc = BSTR_OK;
+    double t_dec = 0, t_chain = 0, t_crc = 0, t_out = 0;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     for (size_t off = 0; off < size && rc == BSTR_OK; off += W) {
         const size_t own = size - off < W ? size - off : W;
         const size_t nb = size - off < W + LA ? size - off : W + LA;
         const bool eof = off + nb == size;
-        if (dev->decode((const uint8_t *)map + off, nb, own, off, eof, st) || dev->chain(*fs, st) || dev->crc_launch(st) || dev->crc_fold(*fs, st)) {
-            say(dev->error()); rc = BSTR_ERR_IO; break;
-        }
+        const double t0 = now();
+        int bad = dev->decode((const uint8_t *)map + off, nb, own, off, eof, st);
+        const double t1 = now();
+        if (!bad) bad = dev->chain(*fs, st);
+        const double t2 = now();
+        if (!bad) bad = dev->crc_launch(st) || dev->crc_fold(*fs, st);
+        const double t3 = now();
+        t_dec += t1 - t0; t_chain += t2 - t1; t_crc += t3 - t2;
+        if (bad) { say(dev->error()); rc = BSTR_ERR_IO; break; }
+        const double t4 = now();
         const uint64_t n = dev->text_bytes();
         if (n > cap_text) {
             cudaFree(d_text); d_text = nullptr;
@@ -331,9 +389,18 @@ extern "C" int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_
                 q += w; left -= (size_t)w;
             }
         }
+        t_out += now() - t4;
         if (fs->ended) break;
     }
     if (rc == BSTR_OK && !fs->ended) { say("unexpected end of compressed data"); rc = BSTR_ERR_IO; }
+    double ku = 0, kd = 0, kp = 0;
+    dev->kernel_ms(&ku, &kd, &kp);
+    if (getenv("BSTR_TRACE"))
+        fprintf(stderr, "[bstr] gunzip_gpu kernels: H2D of the compressed windows %.1f ms, k_decode_ranges %.1f ms, k_propagate %.1f ms\n", ku, kd, kp);
+    if (getenv("BSTR_TRACE"))
+        fprintf(stderr, "[bstr] gunzip_gpu %s: %.1f MB -> %.1f MB | upload+decode %.1f ms, chain+propagate %.1f ms (%llu of %llu ranges decoded again), "
+                "crc %.1f ms, resolve+read back+write %.1f ms\n", path, size / 1e6, fs->out_bytes / 1e6, t_dec, t_chain,
+                (unsigned long long)fs->redone, (unsigned long long)fs->ranges, t_crc, t_out);
     if (stats6) { stats6[0] = size; stats6[1] = fs->out_bytes; stats6[2] = fs->ranges; stats6[3] = fs->ranges - fs->redone; stats6[4] = fs->redone; stats6[5] = fs->members; }
     cudaFree(d_text);
     delete fs;

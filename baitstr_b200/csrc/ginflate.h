@@ -28,6 +28,12 @@ struct FileState {
     FileState() { for (int i = 0; i < 32768; i++) hist[i] = 0; }
 };
 
+// Geometry: the block-start search costs about the same for every range (it ends at the first
+// block, ~half a block in), decoding grows with the range, and history propagation takes one step
+// per range -- so ranges are large, and a window holds enough of them to fill the GPU's ~3000 warp
+// slots (profiles/r02_ginflate_stages.txt).
+constexpr size_t DEFAULT_WINDOW = (size_t)256 << 20, DEFAULT_RANGE = (size_t)128 << 10, LOOK_AHEAD = (size_t)4 << 20;
+
 struct DeviceImpl;
 
 class Device {
@@ -46,6 +52,7 @@ public:
     int resolve(uint8_t *d_text, cudaStream_t st);          // enqueue only
     const char *error() const;
     size_t device_bytes() const;
+    void kernel_ms(double *upload, double *decode, double *propagate) const;   // CUDA-event times summed over the windows so far
 private:
     DeviceImpl *p = nullptr;
 };

@@ -11,8 +11,10 @@
 // in parallel and k_crc_chunks checks every gzip member's CRC-32.  RFC 1951 / RFC 1952 decoding;
 // the table layout follows pinflate.cpp so that both decoders accept the same streams.
 //
-// Decoding is serial per range: lane 0 of the warp walks the Huffman codes (tables of the current
-// block in the warp's slice of shared memory), the other lanes only help with match copies.
+// Decoding is serial per range, and ALL 32 lanes of the warp execute it redundantly: identical
+// instructions on identical data (same addresses: broadcast loads, merged stores), so the extra
+// lanes cost no issue slots -- and a match copy, the one place with per-symbol memory latency, is
+// naturally lane-parallel (lane j copies symbol j): one L2 round trip per match, not one per symbol.
 #pragma once
 #include <stdint.h>
 
@@ -31,7 +33,11 @@ __host__ __device__ inline uint32_t e_val(uint32_t e) { return e >> 16; }
 constexpr int LB = 11, DB = 8, CB = 7;                 // primary index widths: literal/length, distance, code-length code
 constexpr int LIT_CAP = (1 << LB) + 2400, DIST_CAP = (1 << DB) + 2048;
 
-// per-warp shared memory: the two tables of the current block + scratch of the table builder
+// per-range table slot in GLOBAL memory: the two tables of the current block + scratch of the table
+// builder.  Decoding is a serial, latency-bound chain per warp (one active lane), so throughput is
+// resident warps x chain speed: with the tables in shared memory (30 KB per warp) an SM held 7
+// warps; in global memory they stay L1-resident (the kernel carves out no shared memory) and an SM
+// holds 20 (measured: decode stage 3.0 -> see profiles/r02_ginflate_stages.txt)
 struct WarpTables {
     uint32_t lit[LIT_CAP];
     uint32_t dist[DIST_CAP];
@@ -40,7 +46,7 @@ struct WarpTables {
     uint8_t lens[320];
     uint8_t deepest[1 << LB];
 };
-constexpr int WARPS_PER_CTA = 7;                       // 7 x sizeof(WarpTables) = 210 KB of the 227 KB an SM offers
+constexpr int WARPS_PER_CTA = 4;
 
 __constant__ uint16_t c_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
 __constant__ uint8_t c_len_extra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
@@ -246,16 +252,17 @@ struct RangeMeta {                                     // device -> host
 
 __device__ inline bool texty(uint32_t c) { return (c >= 32 && c < 127) || c == '\n' || c == '\t' || c == '\r'; }
 
-// Copy a match of `len` symbols from `dist` back; positions before the start of the run become markers.
+// Copy a match of `len` symbols from `dist` back, the whole warp: symbol j of the match is symbol
+// (j mod dist) of the `dist` symbols before it -- all of which exist before the copy starts, so the
+// lanes are independent.  Positions before the start of the run become markers.
 __device__ inline void copy_match(uint16_t *base, uint16_t *out, uint32_t len, uint32_t dist)
 {
-    const uint32_t have = (uint32_t)(out - base);
-    if (dist > have) {                                               // reaches into the unknown history
-        uint32_t idx = 32768u - (dist - have);
-        while (len && idx < 32768u) { *out++ = (uint16_t)(0x8000u | idx++); len--; }
+    const int have = (int)(out - base);
+    for (uint32_t j = threadIdx.x & 31; j < len; j += 32) {
+        const int t = have - (int)dist + (int)(j < dist ? j : j % dist);
+        out[j] = t < 0 ? (uint16_t)(0x8000u | (uint32_t)(32768 + t)) : base[t];
     }
-    const uint16_t *src = out - dist;
-    for (uint32_t j = 0; j < len; j++) out[j] = src[j];
+    __syncwarp();                                                    // later matches read these symbols from other lanes
 }
 
 template <bool STRICT>
@@ -266,8 +273,8 @@ __device__ inline int inflate_block(BitReader &br, const WarpTables &T, uint16_t
     uint16_t *const lim = base + (cap > SYM_SLACK ? cap - SYM_SLACK : 0);
     for (;;) {
         if (out >= lim) { n = (uint32_t)(out - base); return D_OVERFLOW; }
-        // a length/distance pair needs at most 15 + 5 + 15 + 13 = 48 bits
-        if (br.cnt < 48 && !br.refill()) { n = (uint32_t)(out - base); return D_ERROR; }
+        // a literal/length code needs at most 15 bits; the rest of a length/distance pair is topped up below
+        if (br.cnt < 15 && !br.refill()) { n = (uint32_t)(out - base); return D_ERROR; }
         uint32_t e = T.lit[br.buf & LMASK];
         if ((e & 0x300) == 0) {                                       // K_LIT or K_LIT2: one or two literals
             const uint32_t v = e >> 16;
@@ -287,6 +294,7 @@ __device__ inline int inflate_block(BitReader &br, const WarpTables &T, uint16_t
             continue;
         }
         if (kind == K_BASE) {
+            if (br.cnt < 33 && !br.refill()) { n = (uint32_t)(out - base); return D_ERROR; }     // 5 + 15 + 13 bits to come
             const uint32_t len = e_val(e) + br.take((int)e_extra(e));
             uint32_t d = T.dist[br.buf & DMASK];
             if (e_kind(d) == K_LINK) { br.drop(DB); d = T.dist[e_val(d) + (uint32_t)(br.buf & ((1u << e_extra(d)) - 1))]; }
@@ -346,7 +354,8 @@ __device__ inline int decode_run(const uint8_t *in, uint64_t size, bool at_eof, 
             const uint64_t at = br.bitpos() >> 3;
             if (at + len > size) return D_ERROR;
             if ((uint64_t)n + len + SYM_SLACK > cap) return D_OVERFLOW;
-            for (uint32_t j = 0; j < len; j++) sym[n + j] = in[at + j];
+            for (uint32_t j = threadIdx.x & 31; j < len; j += 32) sym[n + j] = in[at + j];
+            __syncwarp();
             n += len;
             br.init(in, size, (at + len) * 8);
             r = D_OK;
@@ -384,6 +393,10 @@ __device__ inline int decode_run(const uint8_t *in, uint64_t size, bool at_eof, 
     }
 }
 
+// sum of 2^(7-len) over four 3-bit code lengths (len 0 counts nothing): the Kraft sum of the
+// code-length code in five look-ups instead of a 19-trip loop (filled by the host, ginflate.cu)
+__device__ uint16_t g_kraft4[4096];
+
 // ---- block-start search, the whole warp: lane l looks at bit position pos + l --------------------
 // A dynamic block header: BTYPE = 10, HLIT <= 29, HDIST <= 29, and a complete code-length code
 // (Kraft sum of the HCLEN + 4 three-bit lengths = 1).  Returns the first such position in
@@ -403,8 +416,9 @@ __device__ inline uint64_t find_dynamic_block(const uint8_t *in, uint64_t size, 
                 const int hclen = (int)((w >> 13) & 15) + 4;
                 const uint64_t p2 = at + 17;
                 uint64_t v = br.load8(p2 >> 3) >> (p2 & 7);           // >= 57 bits = 19 codes of 3
-                int kraft = 0;
-                for (int i = 0; i < hclen; i++) { const int l = (int)(v & 7); v >>= 3; kraft += l ? 128 >> l : 0; }
+                v &= (1ull << (3 * hclen)) - 1;
+                const int kraft = g_kraft4[v & 4095] + g_kraft4[(v >> 12) & 4095] + g_kraft4[(v >> 24) & 4095] + g_kraft4[(v >> 36) & 4095] +
+                                  g_kraft4[v >> 48];
                 ok = kraft == 128;
             }
         }
@@ -439,20 +453,18 @@ __device__ inline uint64_t find_bgzf_member(const uint8_t *in, uint64_t size, ui
 // One warp per range.  mode 0: search for a block start (dynamic block or bgzip member) in
 // [from_bit, stop_bit) and decode from the first one that passes the strict checks; mode 1: decode
 // from from_bit (a known block start); mode 2: from_bit / 8 is the byte where a gzip header starts.
-__global__ void __launch_bounds__(32 * WARPS_PER_CTA, 1)
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA, 5)
 k_decode_ranges(const uint8_t *__restrict__ in, uint64_t size, int at_eof, const RangeDesc *__restrict__ ranges, int nranges,
-                uint16_t *__restrict__ arena, RangeMeta *__restrict__ meta)
+                uint16_t *__restrict__ arena, RangeMeta *__restrict__ meta, WarpTables *__restrict__ tables)
 {
-    extern __shared__ __align__(16) uint8_t gi_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = blockIdx.x * WARPS_PER_CTA + warp;
     if (r >= nranges) return;
-    WarpTables &T = reinterpret_cast<WarpTables *>(gi_smem)[warp];
+    WarpTables &T = tables[r];
     const RangeDesc d = ranges[r];
     RangeMeta &m = meta[r];
     uint16_t *sym = arena + d.sym_off;
     if (d.mode != 0) {
-        if (lane != 0) return;
         uint64_t bit = d.from_bit;
         int rc = D_OK;
         if (d.mode == 2) {
@@ -460,8 +472,9 @@ k_decode_ranges(const uint8_t *__restrict__ in, uint64_t size, int at_eof, const
             if (!body) rc = D_ERROR;
             bit = body * 8;
         }
-        if (rc == D_OK) rc = decode_run(in, size, at_eof != 0, bit, d.stop_bit, false, T, sym, d.sym_cap, m);
-        m.status = rc;
+        RangeMeta mm;                                          // per lane, identical; lane 0 publishes
+        if (rc == D_OK) rc = decode_run(in, size, at_eof != 0, bit, d.stop_bit, false, T, sym, d.sym_cap, mm);
+        if (lane == 0) { mm.status = rc; m = mm; }
         return;
     }
     uint64_t from = d.from_bit;
@@ -470,10 +483,9 @@ k_decode_ranges(const uint8_t *__restrict__ in, uint64_t size, int at_eof, const
         const uint64_t bg = find_bgzf_member(in, size, from, dyn < d.stop_bit ? dyn : d.stop_bit);     // a bgzip member that starts before it
         const uint64_t c = dyn < bg ? dyn : bg;
         if (c == ~0ull) { if (lane == 0) { m.status = 1; m.n_sym = 0; m.start_bit = m.end_bit = 0; m.n_ends = 0; m.stream_end = 0; } return; }
-        int rc = 0;
-        if (lane == 0) rc = decode_run(in, size, at_eof != 0, c, d.stop_bit, true, T, sym, d.sym_cap, m);
-        rc = __shfl_sync(0xFFFFFFFFu, rc, 0);
-        if (rc == D_OK || rc == D_OVERFLOW || rc == D_UNSUPPORTED) { if (lane == 0) m.status = rc; return; }
+        RangeMeta mm;
+        const int rc = decode_run(in, size, at_eof != 0, c, d.stop_bit, true, T, sym, d.sym_cap, mm);     // all lanes, same result
+        if (rc == D_OK || rc == D_OVERFLOW || rc == D_UNSUPPORTED) { if (lane == 0) { mm.status = rc; m = mm; } return; }
         from = c + 1;                                          // not a block start after all (or broken data: the chain decides)
     }
 }
@@ -485,22 +497,36 @@ struct RunRef { uint64_t sym_off; uint64_t out_off; uint32_t n; uint32_t pad; };
 __global__ void __launch_bounds__(1024, 1)
 k_propagate(const uint16_t *__restrict__ arena, const RunRef *__restrict__ runs, int nruns, uint8_t *hist /* (nruns + 1) x 32768 */)
 {
+    extern __shared__ __align__(16) uint8_t pr_smem[];         // two histories: the gathers of a step stay on chip
+    uint8_t *cur = pr_smem, *nxt = pr_smem + 32768;
+    for (uint32_t i = threadIdx.x * 16; i < 32768u; i += blockDim.x * 16)
+        *reinterpret_cast<uint4 *>(cur + i) = *reinterpret_cast<const uint4 *>(hist + i);
+    __syncthreads();
+    // thread t owns bytes t, t + 1024, ... of every history: consecutive lanes read consecutive symbols
+    // (coalesced), 32 independent loads per thread go out together, then the gathers through the old
+    // history stay in shared memory
     for (int k = 0; k < nruns; k++) {
-        const uint8_t *h = hist + (size_t)k * 32768;
-        uint8_t *o = hist + (size_t)(k + 1) * 32768;
         const uint32_t n = runs[k].n;
         const uint16_t *s = arena + runs[k].sym_off;
-        for (uint32_t i = threadIdx.x; i < 32768u; i += blockDim.x) {
+        uint8_t *o = hist + (size_t)(k + 1) * 32768;
+        uint16_t sy[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+            const uint32_t i = threadIdx.x + 1024u * j;
             // byte i of the new history = byte (n + i - 32768) of (old history ++ run), counted from the run's start
-            uint8_t b;
-            if (n >= 32768u || i >= 32768u - n) {
-                const uint16_t v = s[n - (32768u - i)];
-                b = v < 0x8000u ? (uint8_t)v : h[v & 0x7fffu];
-            } else
-                b = h[i + n];
+            sy[j] = (n >= 32768u || i >= 32768u - n) ? s[n - (32768u - i)] : (uint16_t)0;
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+            const uint32_t i = threadIdx.x + 1024u * j;
+            const bool from_run = n >= 32768u || i >= 32768u - n;
+            const uint32_t v = sy[j];
+            const uint8_t b = (uint8_t)(!from_run ? cur[(i + n) & 0x7fffu] : (v < 0x8000u ? v : cur[v & 0x7fffu]));
+            nxt[i] = b;
             o[i] = b;
         }
         __syncthreads();
+        uint8_t *t = cur; cur = nxt; nxt = t;
     }
 }
 

@@ -222,8 +222,8 @@ int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes,
                 uint64_t *stats6, char *err, size_t errlen);
 
 /* The same for the GPU inflater (csrc/ginflate.cu), which bstr_run_files uses for "*.gz" inputs of
- * some size: the compressed file is cut into windows of window_bytes (0: 64 MiB) and ranges of
- * range_bytes (0: 64 KiB); one warp per range decodes DEFLATE into 16-bit symbols from a guessed
+ * some size: the compressed file is cut into windows of window_bytes (0: 256 MiB) and ranges of
+ * range_bytes (0: 128 KiB); one warp per range decodes DEFLATE into 16-bit symbols from a guessed
  * block start, a chain check accepts the runs, the 32 KiB history is propagated, symbols become
  * bytes and every member's CRC-32 / ISIZE is checked -- all on CUDA device `device`; only the
  * inflated bytes this hook writes to out_fd (-1: discard) come back to the host.  Accepts and rejects
