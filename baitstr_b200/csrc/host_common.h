@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
+#include <functional>
 #include <vector>
 
 #include "../../include/baitstr_select.h"
@@ -48,6 +49,9 @@ struct Lane {
     uint64_t nbytes;
     int final;
     bool busy;
+    // a batch that already lives in device memory (the GPU inflater's text) borrows the slot's input
+    // pointers for one submit/collect; the slot's own buffer is put back afterwards
+    uint8_t *own_in_raw; size_t own_cap_in; bool borrowed;
 };
 
 }  // namespace bstr
@@ -88,7 +92,14 @@ void stream_release(bstr_ctx *ctx);
 int lanes_create(bstr_ctx *ctx);
 void lanes_release(bstr_ctx *ctx);
 int lane_submit(bstr_ctx *ctx, Lane &ln, const uint8_t *raw, uint64_t nbytes, int final);
-int lane_collect(bstr_ctx *ctx, Lane &ln, bstr_batch_out *out);
+// on_state (optional): called once the batch's state is final -- `consumed` input bytes were whole
+// records -- and BEFORE the output is copied back; a non-zero return aborts the collect with that code
+int lane_collect(bstr_ctx *ctx, Lane &ln, bstr_batch_out *out, const std::function<int(uint64_t consumed)> *on_state = nullptr);
+// The batch is d_text[0, nbytes) in the lane's device memory space: 16-byte aligned, IN_SLACK bytes
+// readable before it and IN_SLACK writable bytes after it.  head = its first bytes on the host (tile
+// geometry is estimated from them).  Collect with lane_collect_device.
+int lane_submit_device(bstr_ctx *ctx, Lane &ln, uint8_t *d_text, uint64_t nbytes, int final, const uint8_t *head, size_t head_bytes);
+int lane_collect_device(bstr_ctx *ctx, Lane &ln, bstr_batch_out *out, const std::function<int(uint64_t consumed)> *on_state);
 double estimate_record_bytes(const uint8_t *raw, uint64_t nbytes, double *hdr_bytes);
 int pipeline_stage_count(const bstr_ctx *ctx);
 const char *pipeline_stage_name(const bstr_ctx *ctx, int k);

@@ -37,6 +37,7 @@
 
 #include "host_common.h"
 #include "pinflate.h"
+#include "ginflate.h"
 
 namespace bstr {
 
@@ -50,13 +51,30 @@ struct PinnedBuf {
     size_t cap;
 };
 
+// GPU inflater of one device (csrc/ginflate.cu) + the device buffer its text lands in:
+// [IN_SLACK][carry of the window before | text of this window][IN_SLACK], the batch k_fused_tile reads
+struct GzDevice {
+    ginflate::Device *dev = nullptr;
+    size_t window = 0, range = 0;
+    uint8_t *d_text = nullptr; size_t cap_text = 0;
+};
+
 struct StreamEngine {
     std::vector<PinnedBuf> pool;   // page-locked batch buffers, kept across calls
+    std::vector<GzDevice> gz;      // per entry of bstr_params.devices, created on first use
 };
 
 void stream_release(bstr_ctx *ctx)
 {
     if (!ctx->engine) return;
+    for (size_t d = 0; d < ctx->engine->gz.size(); d++) {
+        GzDevice &g = ctx->engine->gz[d];
+        if (!g.dev && !g.d_text) continue;
+        cudaSetDevice(ctx->p.devices[d]);
+        delete g.dev;
+        cudaFree(g.d_text);
+    }
+    cudaSetDevice(ctx->dev);
     for (auto &b : ctx->engine->pool) if (b.p) cudaFreeHost(b.p);
     delete ctx->engine;
     ctx->engine = nullptr;
@@ -225,6 +243,22 @@ static size_t record_cut(const uint8_t *buf, size_t have)
     return (size_t)(q - buf) + 1;
 }
 
+// One "*.gz" input that goes through the GPU inflater.  Its windows are separate jobs that any
+// device may take; what links them lives here, in host memory: where the next run must start, the
+// last 32 KiB of text and the CRC of the open member (ginflate::FileState), and the partial record
+// at the end of a window, which is the head of the next window's batch.  The two ordered stages of
+// a window (chain, scan) take turns by window number.
+struct GzFile {
+    const uint8_t *map = nullptr; size_t size = 0;
+    ginflate::FileState fs;
+    std::mutex mu; std::condition_variable cv;
+    int chain_turn = 0, scan_turn = 0;
+    std::vector<uint8_t> carry;
+    bool failed = false;
+    std::atomic<int> refs{0};
+    ~GzFile() { if (map) munmap((void *)map, size); }
+};
+
 // One batch travelling reader -> device worker -> writer.
 struct Job {
     uint64_t seq;
@@ -236,7 +270,15 @@ struct Job {
     int rc, lane;
     bstr_batch_out bo;
     char msg[512];
+    // a window of a .gz file for the GPU inflater: file bytes [gz_off, gz_off + gz_nb), the first gz_own its own
+    GzFile *gz; size_t gz_off, gz_nb, gz_own; bool gz_eof; int gz_w;
 };
+
+static void job_free(Job *j)
+{
+    if (j->gz && j->gz->refs.fetch_sub(1) == 1) delete j->gz;
+    delete j;
+}
 
 struct Pipeline {
     bstr_ctx *ctx;
@@ -254,6 +296,9 @@ struct Pipeline {
     int n_readers = 4;                    // host threads the caller allows (bstr_params.host_threads, at least 4)
     int plain_readers = 4;                // threads that read one plain file in parallel segments
     int gz_decoders = 4, gz_fillers = 2, gz_pending = 3;   // parallel inflate: decoder threads, segment producers, segments decoded ahead
+    bool gpu_inflate = true;              // "*.gz" files of some size go through the GPU inflater (BSTR_GPU_INFLATE=0: host threads)
+    uint64_t gz_gpu_min = 8u << 20;       // ... from this compressed size on
+    size_t gz_window = 0, gz_range = 0;   // its geometry (BSTR_GZ_WINDOW / BSTR_GZ_RANGE, bytes)
     double t_read = 0, t_cut = 0, t_alloc = 0, t_bufwait = 0;   // reader threads, ms, summed (BSTR_TRACE)
     bool abort_seen() { std::lock_guard<std::mutex> g(mu); return abort; }
 };
@@ -553,6 +598,35 @@ static void reader_main(Pipeline *pp)
             fi = fj - 1;
             continue;
         }
+        if (src.is_gz && P.gpu_inflate) {
+            // a regular .gz file of some size: the GPU inflater (ginflate.h).  The file is mapped and
+            // cut into windows; every window is a job of its own, so the windows of ONE file are dealt
+            // to all GPUs, and the inflated text never visits the host.
+            const int fd = open(P.paths[fi], O_RDONLY);
+            bool done = false;
+            if (fd >= 0 && fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && (uint64_t)sb.st_size >= P.gz_gpu_min) {
+                void *m = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+                if (m != MAP_FAILED) {
+                    madvise(m, (size_t)sb.st_size, MADV_SEQUENTIAL);
+                    GzFile *gz = new GzFile();
+                    gz->map = (const uint8_t *)m; gz->size = (size_t)sb.st_size;
+                    const size_t W = P.gz_window, LA = ginflate::LOOK_AHEAD;
+                    const int nw = (int)((gz->size + W - 1) / W);
+                    gz->refs = nw;
+                    for (int w = 0; w < nw; w++) {
+                        Job *j = new_job(fi, PinnedBuf{nullptr, 0}, 0, w == nw - 1, w == nw - 1);
+                        j->gz = gz; j->gz_w = w; j->gz_off = (size_t)w * W;
+                        j->gz_own = gz->size - j->gz_off < W ? gz->size - j->gz_off : W;
+                        j->gz_nb = gz->size - j->gz_off < W + LA ? gz->size - j->gz_off : W + LA;
+                        j->gz_eof = j->gz_off + j->gz_nb == gz->size;
+                        emit(P, j);
+                    }
+                    done = true;
+                }
+            }
+            if (fd >= 0) close(fd);
+            if (done) { src.close_all(); continue; }
+        }
         if (src.is_gz && P.n_readers > 1 && P.buf_cap >= (4u << 20) && !getenv("BSTR_SERIAL_INFLATE")) {
             // a regular .gz file of some size: inflate it on all reader threads (pinflate.h)
             const int fd = open(P.paths[fi], O_RDONLY);
@@ -653,6 +727,102 @@ static void publish(Pipeline &P, Job *j)
     P.cv_done.notify_all();
 }
 
+// One window of a .gz file on device d, lane `lane`: all stages of ginflate.h, then k_fused_tile over
+// [carry of the window before | this window's text] straight from device memory.  The stages that
+// must go in window order (chain, scan) wait for their turn on the file's GzFile; everything else
+// -- the upload, the decoding of all ranges, the CRC kernel, the copy of the output -- overlaps with
+// the other windows of the file on the other GPUs.  Fills j->rc / j->bo / j->msg.
+static void gz_window_job(Pipeline &P, int d, int lane, Job *j)
+{
+    bstr_ctx *ctx = P.ctx;
+    Lane &ln = ctx->lanes[lane];
+    GzFile &gz = *j->gz;
+    GzDevice &G = ctx->engine->gz[(size_t)d];
+    bool turn_released = false;
+    auto fail = [&](int rc, const char *msg) {
+        j->rc = rc;
+        snprintf(j->msg, sizeof(j->msg), "read error on %.300s: %.180s", P.paths[j->file], msg);
+        { std::lock_guard<std::mutex> g(gz.mu); gz.failed = true; }
+        gz.cv.notify_all();
+    };
+    auto wait_turn = [&](const int &turn) -> bool {
+        std::unique_lock<std::mutex> lk(gz.mu);
+        while (turn != j->gz_w && !gz.failed) {
+            if (gz.cv.wait_for(lk, std::chrono::milliseconds(50)) == std::cv_status::timeout) {
+                lk.unlock();
+                const bool ab = P.abort_seen();
+                lk.lock();
+                if (ab) return false;
+            }
+        }
+        return !gz.failed;
+    };
+    auto next_turn = [&](int &turn) { { std::lock_guard<std::mutex> g(gz.mu); turn++; } gz.cv.notify_all(); };
+    if (cudaSetDevice(ln.dev) != cudaSuccess) { cudaGetLastError(); return fail(BSTR_ERR_CUDA, "cudaSetDevice failed"); }
+    if (!G.dev || G.window != P.gz_window || G.range != P.gz_range) {
+        delete G.dev;
+        char err[256] = "";
+        G.dev = ginflate::Device::create(P.gz_window, ginflate::LOOK_AHEAD, P.gz_range, err, sizeof(err));
+        G.window = P.gz_window; G.range = P.gz_range;
+        if (!G.dev) return fail(BSTR_ERR_CUDA, err);
+    }
+    const double t0 = now_ms();
+    if (G.dev->decode(gz.map + j->gz_off, j->gz_nb, j->gz_own, j->gz_off, j->gz_eof, ln.st)) return fail(BSTR_ERR_IO, G.dev->error());
+    const double t1 = now_ms();
+    if (!wait_turn(gz.chain_turn)) return fail(BSTR_ERR_IO, "an earlier part of the file failed");
+    const double t2 = now_ms();
+    if (G.dev->chain(gz.fs, ln.st)) return fail(BSTR_ERR_IO, G.dev->error());
+    next_turn(gz.chain_turn);
+    const double t3 = now_ms();
+    if (G.dev->crc_launch(ln.st)) return fail(BSTR_ERR_IO, G.dev->error());
+    if (!wait_turn(gz.scan_turn)) return fail(BSTR_ERR_IO, "an earlier part of the file failed");
+    const double t4 = now_ms();
+    if (G.dev->crc_fold(gz.fs, ln.st)) return fail(BSTR_ERR_IO, G.dev->error());
+    const uint64_t tn = G.dev->text_bytes();
+    const size_t cn = gz.carry.size();
+    const uint64_t total = cn + tn;
+    if (total > (2ull << 30)) return fail(BSTR_ERR_TOO_LARGE, "a window of the file inflates to more than 2 GiB (set BSTR_GZ_WINDOW to a smaller value)");
+    if (2 * IN_SLACK + total > G.cap_text) {
+        cudaFree(G.d_text); G.d_text = nullptr; G.cap_text = 0;
+        const size_t cap = (size_t)(2 * IN_SLACK + total + total / 4 + (1u << 20));
+        if (cudaMalloc((void **)&G.d_text, cap) != cudaSuccess) { cudaGetLastError(); return fail(BSTR_ERR_CUDA, "out of device memory for the inflated window"); }
+        G.cap_text = cap;
+    }
+    uint8_t *base = G.d_text + IN_SLACK;
+    std::vector<uint8_t> head((size_t)(total < (128u << 10) ? total : (128u << 10)));
+    bool ok = cudaMemsetAsync(G.d_text, 0, IN_SLACK, ln.st) == cudaSuccess;
+    if (ok && cn) ok = cudaMemcpyAsync(base, gz.carry.data(), cn, cudaMemcpyHostToDevice, ln.st) == cudaSuccess;
+    if (ok) ok = G.dev->resolve(base + cn, ln.st) == 0;
+    if (ok && !head.empty()) ok = cudaMemcpyAsync(head.data(), base, head.size(), cudaMemcpyDeviceToHost, ln.st) == cudaSuccess;
+    if (ok) ok = cudaStreamSynchronize(ln.st) == cudaSuccess;
+    if (!ok) { cudaGetLastError(); return fail(BSTR_ERR_CUDA, G.dev->error()[0] ? G.dev->error() : "CUDA error while the window's text was put together"); }
+    int rc = lane_submit_device(ctx, ln, base, total, j->final ? 1 : 0, head.data(), head.size());
+    if (rc == BSTR_OK) {
+        const std::function<int(uint64_t)> on_state = [&](uint64_t consumed) -> int {
+            // what follows the last whole record is the head of the next window's batch
+            const uint64_t rest = total - (consumed < total ? consumed : total);
+            if (rest > (256u << 20)) { set_error(ctx, "a record of more than 256 MiB"); return BSTR_ERR_TOO_LARGE; }
+            gz.carry.resize((size_t)rest);
+            if (rest && cudaMemcpy(gz.carry.data(), base + consumed, (size_t)rest, cudaMemcpyDeviceToHost) != cudaSuccess)
+                return cuda_fail(ctx, cudaGetLastError(), "carry read-back", __LINE__);
+            next_turn(gz.scan_turn);
+            turn_released = true;
+            return BSTR_OK;
+        };
+        rc = lane_collect_device(ctx, ln, &j->bo, &on_state);
+    }
+    const double t5 = now_ms();
+    if (rc != BSTR_OK) {
+        j->rc = rc;
+        { std::lock_guard<std::mutex> g(*(std::mutex *)ctx->lock); snprintf(j->msg, sizeof(j->msg), "%s", ctx->err); }
+        if (!turn_released) { { std::lock_guard<std::mutex> g(gz.mu); gz.failed = true; } gz.cv.notify_all(); }
+        return;
+    }
+    if (getenv("BSTR_TRACE"))
+        fprintf(stderr, "[bstr] gz window %d of %s on device %d: %.1f MB -> %.1f MB | upload+decode %.1f ms, wait %.1f, chain %.1f, crc+wait %.1f, "
+                "text+scan+output %.1f ms\n", j->gz_w, P.paths[j->file], ln.dev, j->gz_own / 1e6, tn / 1e6, t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4);
+}
+
 // One thread per GPU: keeps up to BSTR_LANES_PER_DEVICE batches in flight on its device.
 static void device_main(Pipeline *pp, int d)
 {
@@ -681,11 +851,20 @@ static void device_main(Pipeline *pp, int d)
                 bstr_batch_out bo;
                 lane_collect(ctx, ctx->lanes[it.first], &bo);
                 put_buf(P, it.second->buf);
-                delete it.second;
+                job_free(it.second);
             }
             return;
         }
         if (quit) return;
+        if (job && job->gz) {                                       // a window of a .gz file: GPU inflater + scan, all on this device
+            gz_window_job(P, d, lane, job);
+            const bool hold = job->rc == BSTR_OK && job->bo.out_bytes;
+            job->lane = hold ? lane : -1;
+            ctx->lanes[lane].busy = false;
+            { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = hold ? 2 : 0; }
+            publish(P, job);
+            continue;
+        }
         if (job) {
             if (job->reader_error || job->nbytes == 0) {            // nothing for the GPU
                 put_buf(P, job->buf); job->buf.p = nullptr;
@@ -749,6 +928,16 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     P.gz_fillers = knob("BSTR_GZ_FILLERS", P.n_readers >= 8 ? 3 : 2);        // resolve markers, CRC-32, newline count
     P.gz_decoders = knob("BSTR_GZ_DECODERS", P.n_readers - P.gz_fillers);    // together they use the host threads allowed
     P.gz_pending = knob("BSTR_GZ_PENDING", 6);
+    {
+        const char *gi = getenv("BSTR_GPU_INFLATE");
+        P.gpu_inflate = !(gi && gi[0] == '0');
+        const char *gm = getenv("BSTR_GZ_GPU_MIN"), *gw = getenv("BSTR_GZ_WINDOW"), *gr = getenv("BSTR_GZ_RANGE");
+        if (gm && atoll(gm) >= 0) P.gz_gpu_min = (uint64_t)atoll(gm);
+        P.gz_window = gw && atoll(gw) > 0 ? (size_t)atoll(gw) : ginflate::DEFAULT_WINDOW;
+        P.gz_range = gr && atoll(gr) > 0 ? (size_t)atoll(gr) : ginflate::DEFAULT_RANGE;
+        if (P.gz_window < P.gz_range) P.gz_window = P.gz_range;
+        if (ctx->engine->gz.size() != (size_t)ctx->p.n_devices) ctx->engine->gz.resize((size_t)ctx->p.n_devices);
+    }
     P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)(P.plain_readers > P.gz_fillers ? P.plain_readers : P.gz_fillers);
     P.lane_state.assign((size_t)ctx->n_lanes, 0);
     for (auto &b : ctx->engine->pool) {
@@ -795,7 +984,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
             P.cv_work.notify_all();
         }
         t_write += now_ms() - tx0;
-        if (result) { delete j; break; }
+        if (result) { job_free(j); break; }
         rec_base += j->bo.n_records;
         if (j->file_end) {
             rec_base = 0;
@@ -805,7 +994,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
                 if (n > 0) write_all(err_fd, (const uint8_t *)line, (size_t)n);
             }
         }
-        delete j;
+        job_free(j);
         next++;
     }
     if (result) {
@@ -814,8 +1003,8 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     }
     reader.join();
     for (auto &w : workers) w.join();
-    for (Job *j : P.work) { if (j->buf.p) put_buf(P, j->buf); delete j; }
-    for (auto &kv : P.done) { if (kv.second->buf.p) put_buf(P, kv.second->buf); delete kv.second; }
+    for (Job *j : P.work) { if (j->buf.p) put_buf(P, j->buf); job_free(j); }
+    for (auto &kv : P.done) { if (kv.second->buf.p) put_buf(P, kv.second->buf); job_free(kv.second); }
     for (auto &b : P.free_bufs) ctx->engine->pool.push_back(b);
     for (int l = 0; l < ctx->n_lanes; l++) ctx->lanes[l].busy = false;
     CUDA_TRY(cudaSetDevice(ctx->dev));

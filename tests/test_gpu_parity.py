@@ -580,6 +580,74 @@ def test_run_files_runs_of_plain_files(capi, tmp_path):
     assert got.startswith(sel[0]) and (sel[0] + sel[1]).startswith(got[:len(sel[0]) + 1000]) and len(got) < len(sel[0] + sel[1])
 
 
+def test_run_files_gpu_inflate(capi, tmp_path, monkeypatch):
+    """'*.gz' inputs through the GPU inflater (csrc/ginflate.cu) inside bstr_run_files: the file is
+    cut into windows, every window is inflated on the device and scanned straight from device
+    memory; a record that straddles two windows travels as the carry.  Geometry is forced small so
+    that a few MB of gz span many windows.  Same bytes as the oracle on the inflated text, for
+    single-member, multi-member and bgzip files, a file without final newline, mixed with plain
+    files; corrupt data and a bad record in a late window fail loudly, the output before is kept."""
+    import gzip
+    from tests.test_inflate_cpu import bgzf
+    monkeypatch.setenv("BSTR_GZ_GPU_MIN", "0")
+    monkeypatch.setenv("BSTR_GZ_WINDOW", str(768 << 10))
+    monkeypatch.setenv("BSTR_GZ_RANGE", str(32 << 10))
+    a = util.synth_fastq(40000, 100, seed=301, tag="ga", p_str=0.5)
+    b = util.synth_fastq(25000, 150, seed=302, tag="gb", vary_len=True)[:-1]      # no final newline
+    c = util.synth_fastq(3000, 76, seed=303, tag="gc")
+    files = {"a.fq.gz": gzip.compress(a, 1), "b.fq.gz": gzip.compress(b, 6), "c.fq": c,
+             "a_bgzf.fq.gz": bgzf(a), "a_multi.fq.gz": gzip.compress(a[:1_000_003], 9) + gzip.compress(a[1_000_003:], 1)}
+    paths = {}
+    for name, data in files.items():
+        paths[name] = str(tmp_path / name)
+        open(paths[name], "wb").write(data)
+    sa, sb, sc = oracle.select_buffer(a), oracle.select_buffer(b), oracle.select_buffer(c)
+    order = ["a.fq.gz", "c.fq", "b.fq.gz", "a_bgzf.fq.gz", "a_multi.fq.gz"]
+    want = sa + sc + sb + sa + sa
+    outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+    for threads in (0, 3):
+        with capi.Context(host_threads=threads) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
+            ctx.run_files([paths[n] for n in order], out_fd=fo.fileno(), err_fd=fe.fileno())
+            st = ctx.stats()
+            # and once more on the same context (the inflater's working set is kept)
+            with open(outp + "2", "wb") as fo2:
+                ctx.run_files([paths["b.fq.gz"]], out_fd=fo2.fileno(), err_fd=-1)
+        assert open(outp, "rb").read() == want
+        assert open(outp + "2", "rb").read() == sb
+        assert open(errp).read() == "".join("Done processing %s\n" % paths[n] for n in order)
+        assert st["records"] == 3 * 40000 + 25000 + 3000 and st["batches"] >= 12      # several windows per .gz file
+    # the host inflater gives the same bytes (BSTR_GPU_INFLATE=0)
+    monkeypatch.setenv("BSTR_GPU_INFLATE", "0")
+    with capi.Context() as ctx, open(outp, "wb") as fo:
+        ctx.run_files([paths["a.fq.gz"], paths["b.fq.gz"]], out_fd=fo.fileno(), err_fd=-1)
+    assert open(outp, "rb").read() == sa + sb
+    monkeypatch.delenv("BSTR_GPU_INFLATE")
+    # corrupt deflate data in the middle, a wrong CRC, a truncated file: I/O errors; what was written is a prefix
+    z = bytearray(files["a.fq.gz"]); z[len(z) // 2] ^= 0x20
+    zc = bytearray(files["a.fq.gz"]); zc[-6] ^= 1
+    for k, bad in enumerate((bytes(z), bytes(zc), files["a.fq.gz"][:len(z) * 2 // 3])):
+        pb = str(tmp_path / "bad.fq.gz")
+        open(pb, "wb").write(bad)
+        with capi.Context() as ctx, open(outp, "wb") as fo:
+            with pytest.raises(capi.BstrError) as ei:
+                ctx.run_files([paths["c.fq"], pb, paths["c.fq"]], out_fd=fo.fileno(), err_fd=-1)
+            assert ei.value.code == -4 and "bad.fq.gz" in str(ei.value)
+        got = open(outp, "rb").read()
+        # (a flipped bit may decode to valid but wrong bytes that only the member's CRC catches at the
+        # end -- windows before it are out by then, as the reference prints the chunks before gzip raises)
+        assert got.startswith(sc) and (k == 0 or (sc + sa).startswith(got))
+    # a bad record deep in the file (a late window): the error names the record index in the FILE
+    lines = a.split(b"\n")
+    lines[4 * 33333 + 2] = b"-"
+    open(paths["a.fq.gz"], "wb").write(gzip.compress(b"\n".join(lines), 1))
+    with capi.Context() as ctx, open(outp, "wb") as fo:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.run_files([paths["a.fq.gz"]], out_fd=fo.fileno(), err_fd=-1)
+        assert ei.value.code == -12 and "record 33333" in str(ei.value)
+    got = open(outp, "rb").read()
+    assert sa.startswith(got) and 0 < len(got) < len(sa)
+
+
 def test_run_files_parallel_inflate(capi, tmp_path):
     """'*.gz' inputs of some size are inflated on several threads (pinflate.cpp) and fed to the GPU
     in segments stitched at record boundaries: same bytes as the oracle for a single-member file,
@@ -670,8 +738,13 @@ def test_multi_gpu_run_files_byte_identical(capi, tmp_path):
     want = b"".join(oracle.select_buffer(r) for r in shards)
     done = "".join("Done processing %s\n" % q for q in plain)
     devs = list(range(ndev))
-    for files, bb in ((plain, 0), (plain, 256 << 10), (gz, 4 << 20), (plain, 4 << 20)):
+    for files, bb in ((plain, 0), (plain, 256 << 10), (gz, 4 << 20), (plain, 4 << 20), (gz, -1)):
         outp, errp = str(tmp_path / "o.fq"), str(tmp_path / "e.txt")
+        if bb == -1:            # the GPU inflater: the windows of every .gz shard are dealt to all GPUs
+            bb = 0
+            os.environ.update(BSTR_GZ_GPU_MIN="0", BSTR_GZ_WINDOW=str(512 << 10), BSTR_GZ_RANGE=str(32 << 10))
+        else:
+            os.environ["BSTR_GPU_INFLATE"] = "0"
         with capi.Context(devices=devs, batch_bytes=bb, host_threads=8) as ctx, open(outp, "wb") as fo, open(errp, "wb") as fe:
             assert ctx.lanes() == 3 * ndev
             ctx.run_files(files, out_fd=fo.fileno(), err_fd=fe.fileno())
@@ -680,7 +753,9 @@ def test_multi_gpu_run_files_byte_identical(capi, tmp_path):
         if files is plain:
             assert open(errp).read() == done
         assert sum(st["device_batches"]) == st["batches"]
-        if bb == 256 << 10:                                   # ~ 30 batches per shard: every GPU must have had work
+        for k in ("BSTR_GZ_GPU_MIN", "BSTR_GZ_WINDOW", "BSTR_GZ_RANGE", "BSTR_GPU_INFLATE"):
+            os.environ.pop(k, None)
+        if bb == 256 << 10 or files is gz and bb == 0:        # many batches / windows per shard: every GPU must have had work
             assert all(n > 0 for n in st["device_batches"][:ndev]), st["device_batches"]
     # the lanes API on several devices: lane l lives on device l % ndev
     with capi.Context(devices=devs) as ctx:
