@@ -59,9 +59,10 @@ struct GzDevice {
     uint8_t *d_text = nullptr; size_t cap_text = 0;
 };
 
+constexpr int GZ_PAR = 2;          // .gz windows in flight per device: one decodes while the other uploads / chains / scans
 struct StreamEngine {
     std::vector<PinnedBuf> pool;   // page-locked batch buffers, kept across calls
-    std::vector<GzDevice> gz;      // per entry of bstr_params.devices, created on first use
+    std::vector<GzDevice> gz;      // GZ_PAR per entry of bstr_params.devices, created on first use
 };
 
 void stream_release(bstr_ctx *ctx)
@@ -70,7 +71,7 @@ void stream_release(bstr_ctx *ctx)
     for (size_t d = 0; d < ctx->engine->gz.size(); d++) {
         GzDevice &g = ctx->engine->gz[d];
         if (!g.dev && !g.d_text) continue;
-        cudaSetDevice(ctx->p.devices[d]);
+        cudaSetDevice(ctx->p.devices[d / GZ_PAR]);
         delete g.dev;
         cudaFree(g.d_text);
     }
@@ -732,12 +733,12 @@ static void publish(Pipeline &P, Job *j)
 // must go in window order (chain, scan) wait for their turn on the file's GzFile; everything else
 // -- the upload, the decoding of all ranges, the CRC kernel, the copy of the output -- overlaps with
 // the other windows of the file on the other GPUs.  Fills j->rc / j->bo / j->msg.
-static void gz_window_job(Pipeline &P, int d, int lane, Job *j)
+static void gz_window_job(Pipeline &P, int d, int slot, int lane, Job *j)
 {
     bstr_ctx *ctx = P.ctx;
     Lane &ln = ctx->lanes[lane];
     GzFile &gz = *j->gz;
-    GzDevice &G = ctx->engine->gz[(size_t)d];
+    GzDevice &G = ctx->engine->gz[(size_t)d * GZ_PAR + (size_t)slot];
     bool turn_released = false;
     auto fail = [&](int rc, const char *msg) {
         j->rc = rc;
@@ -830,9 +831,13 @@ static void device_main(Pipeline *pp, int d)
     bstr_ctx *ctx = P.ctx;
     const int ndev = ctx->p.n_devices;
     std::deque<std::pair<int, Job *>> inflight;
+    // windows of .gz files run on threads of their own, at most GZ_PAR per device (gz_busy: P.mu)
+    std::vector<std::thread> gz_threads;
+    bool gz_busy[GZ_PAR] = {false};
+    auto join_gz = [&]() { for (auto &t : gz_threads) t.join(); gz_threads.clear(); };
     for (;;) {
         Job *job = nullptr;
-        int lane = -1;
+        int lane = -1, gz_slot = -1;
         bool quit = false, aborting = false;
         {
             std::unique_lock<std::mutex> lk(P.mu);
@@ -840,9 +845,19 @@ static void device_main(Pipeline *pp, int d)
                 if (P.abort) { aborting = true; break; }
                 lane = -1;
                 for (int l = d; l < ctx->n_lanes; l += ndev) if (P.lane_state[l] == 0) { lane = l; break; }
-                if (lane >= 0 && !P.work.empty()) { job = P.work.front(); P.work.pop_front(); P.lane_state[lane] = 1; break; }
+                if (lane >= 0 && !P.work.empty()) {
+                    gz_slot = -1;
+                    if (P.work.front()->gz) for (int g = 0; g < GZ_PAR; g++) if (!gz_busy[g]) { gz_slot = g; break; }
+                    if (!P.work.front()->gz || gz_slot >= 0) {
+                        job = P.work.front(); P.work.pop_front(); P.lane_state[lane] = 1;
+                        if (gz_slot >= 0) gz_busy[gz_slot] = true;
+                        break;
+                    }
+                }
                 if (!inflight.empty()) break;                       // nothing to submit: collect the oldest
-                if (P.reader_finished && P.work.empty()) { quit = true; break; }
+                bool gz_running = false;
+                for (int g = 0; g < GZ_PAR; g++) gz_running |= gz_busy[g];
+                if (P.reader_finished && P.work.empty() && !gz_running) { quit = true; break; }
                 P.cv_work.wait(lk);
             }
         }
@@ -853,16 +868,20 @@ static void device_main(Pipeline *pp, int d)
                 put_buf(P, it.second->buf);
                 job_free(it.second);
             }
+            join_gz();
             return;
         }
-        if (quit) return;
+        if (quit) { join_gz(); return; }
         if (job && job->gz) {                                       // a window of a .gz file: GPU inflater + scan, all on this device
-            gz_window_job(P, d, lane, job);
-            const bool hold = job->rc == BSTR_OK && job->bo.out_bytes;
-            job->lane = hold ? lane : -1;
-            ctx->lanes[lane].busy = false;
-            { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = hold ? 2 : 0; }
-            publish(P, job);
+            gz_threads.emplace_back([&P, ctx, d, gz_slot, lane, job, &gz_busy]() {
+                gz_window_job(P, d, gz_slot, lane, job);
+                const bool hold = job->rc == BSTR_OK && job->bo.out_bytes;
+                job->lane = hold ? lane : -1;
+                ctx->lanes[lane].busy = false;
+                { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = hold ? 2 : 0; gz_busy[gz_slot] = false; }
+                publish(P, job);
+                P.cv_work.notify_all();
+            });
             continue;
         }
         if (job) {
@@ -936,7 +955,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
         P.gz_window = gw && atoll(gw) > 0 ? (size_t)atoll(gw) : ginflate::DEFAULT_WINDOW;
         P.gz_range = gr && atoll(gr) > 0 ? (size_t)atoll(gr) : ginflate::DEFAULT_RANGE;
         if (P.gz_window < P.gz_range) P.gz_window = P.gz_range;
-        if (ctx->engine->gz.size() != (size_t)ctx->p.n_devices) ctx->engine->gz.resize((size_t)ctx->p.n_devices);
+        if (ctx->engine->gz.size() != (size_t)ctx->p.n_devices * GZ_PAR) ctx->engine->gz.resize((size_t)ctx->p.n_devices * GZ_PAR);
     }
     P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)(P.plain_readers > P.gz_fillers ? P.plain_readers : P.gz_fillers);
     P.lane_state.assign((size_t)ctx->n_lanes, 0);
