@@ -17,6 +17,9 @@ namespace ginflate {
 // crc(A) * x^(8 |B|) mod P  xor  crc(B) over GF(2), bit-reflected polynomial 0xEDB88320.  The operator
 // x^(8 n) mod P for the fixed chunk length is computed once.
 constexpr uint32_t CRC_CHUNK = 8u << 10;
+constexpr size_t TARGET_RANGES = 2800;          // ~ the warps a B200 holds for k_decode_ranges (148 SMs x 20)
+constexpr size_t MIN_RANGE = 16u << 10;
+constexpr size_t SYM_EXTRA = 256u << 10;        // symbols a range may produce beyond 10x its size (the block that straddles its end)
 static uint32_t gf2_multmodp(uint32_t a, uint32_t b)
 {
     uint32_t m = 1u << 31, p = 0;
@@ -85,12 +88,13 @@ Device *Device::create(size_t window_bytes, size_t look_ahead, size_t range_byte
     if (range_bytes < 4096) range_bytes = 4096;
     if (window_bytes < range_bytes) window_bytes = range_bytes;
     p->window_bytes = window_bytes; p->look_ahead = look_ahead; p->range_bytes = range_bytes;
-    p->max_ranges = (int)((window_bytes + range_bytes - 1) / range_bytes);
-    p->sym_cap = (uint32_t)(range_bytes * 10 + (256u << 10));
+    const size_t full = (window_bytes + range_bytes - 1) / range_bytes;         // ranges of a full window
+    p->max_ranges = (int)(full > TARGET_RANGES + 256 ? full : TARGET_RANGES + 256); // a short window is cut into smaller ranges (decode)
+    p->sym_cap = (uint32_t)(range_bytes * 10 + SYM_EXTRA);
     cudaError_t e;
     p->cap_comp = window_bytes + look_ahead + 64;
     if ((e = cudaMalloc((void **)&p->d_comp, p->cap_comp)) != cudaSuccess) return bail("window buffer", e);
-    p->cap_arena = (size_t)p->max_ranges * p->sym_cap;
+    p->cap_arena = full * p->sym_cap;
     if ((e = cudaMalloc((void **)&p->d_arena, p->cap_arena * sizeof(uint16_t))) != cudaSuccess) return bail("symbol arena", e);
     const size_t nr = (size_t)p->max_ranges + 2;
     if ((e = cudaMalloc((void **)&p->d_desc, nr * sizeof(RangeDesc))) != cudaSuccess) return bail("range table", e);
@@ -152,14 +156,23 @@ int Device::decode(const uint8_t *comp, size_t nbytes, size_t own_bytes, uint64_
     cudaEventRecord(p->ev[0], st);
     GI_TRY(cudaMemcpyAsync(p->d_comp, comp, nbytes, cudaMemcpyHostToDevice, st));
     GI_TRY(cudaMemsetAsync(p->d_comp + nbytes, 0, 64, st));
-    const size_t R = p->range_bytes;
+    // a window shorter than a full one (small files, the last window) is cut into smaller ranges, so that
+    // there still are ~TARGET_RANGES warps: decoding is a serial chain per warp, its time is the size of a range
+    size_t R = (own_bytes + TARGET_RANGES - 1) / TARGET_RANGES;
+    R = (R + 4095) & ~(size_t)4095;
+    if (R < MIN_RANGE) R = MIN_RANGE;
+    if (R > p->range_bytes) R = p->range_bytes;
     p->nranges = (int)((own_bytes + R - 1) / R);
     if (p->nranges == 0) p->nranges = 1;
+    if (p->nranges > p->max_ranges) return p->fail("GPU inflater: too many ranges");
+    size_t cap = R * 10 + SYM_EXTRA;
+    if (cap * (size_t)p->nranges > p->cap_arena) cap = p->cap_arena / (size_t)p->nranges;
+    cap &= ~(size_t)7;
     for (int r = 0; r < p->nranges; r++) {
         RangeDesc &d = p->h_desc[r];
         const uint64_t lo = (uint64_t)r * R, hi = (uint64_t)(r + 1) * R < own_bytes ? (uint64_t)(r + 1) * R : own_bytes;
         d.from_bit = lo * 8; d.stop_bit = hi * 8;
-        d.sym_off = (uint64_t)r * p->sym_cap; d.sym_cap = p->sym_cap;
+        d.sym_off = (uint64_t)r * cap; d.sym_cap = (uint32_t)cap;
         d.mode = (r == 0 && file_off == 0) ? 2 : 0;
     }
     GI_TRY(cudaMemcpyAsync(p->d_desc, p->h_desc, (size_t)p->nranges * sizeof(RangeDesc), cudaMemcpyHostToDevice, st));

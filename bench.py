@@ -427,7 +427,8 @@ def multi_gpu_leg(ndev, reads_per_shard):
         res["oracle_prefix"] = {"reads": npre, "identical": prefix_ok}
         ok = prefix_ok
         devs = list(range(ndev))
-        for tag, files, bb, rep in (("plain", plain, 0, 2), ("plain_1MiB_batches", plain, 1 << 20, 1), ("gz", gz, 0, 2)):
+        # (.gz: the first passes allocate the page-locked output buffers of fresh lanes and the inflater's working sets)
+        for tag, files, bb, rep in (("plain", plain, 0, 2), ("plain_1MiB_batches", plain, 1 << 20, 1), ("gz", gz, 0, 4)):
             outp, dt, dt_file, st = run(devs, files, bb, tag, rep)
             same = file_md5(outp) == ref_md5 and os.path.getsize(outp) == os.path.getsize(ref_out)
             ok = ok and same
