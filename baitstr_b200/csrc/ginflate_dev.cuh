@@ -265,12 +265,88 @@ __device__ inline void copy_match(uint16_t *base, uint16_t *out, uint32_t len, u
     __syncwarp();                                                    // later matches read these symbols from other lanes
 }
 
+// The symbols of one block.  The hot loop does not shift a 64-bit buffer (two SHF per shift here):
+// it keeps three consecutive 32-bit words of the input (the third is the prefetch) and a bit offset,
+// and takes a 32-bit window with ONE funnel shift -- enough for a literal/length code with its extra
+// bits (15 + 5) and, after re-normalising, for a distance code with its extra bits (15 + 13).  The
+// last bytes of the input (and everything the fast loop does not like) go through the careful
+// BitReader loop below, which is the same code as before.
 template <bool STRICT>
 __device__ inline int inflate_block(BitReader &br, const WarpTables &T, uint16_t *base, uint32_t &n, uint32_t cap)
 {
     const uint32_t LMASK = (1u << LB) - 1, DMASK = (1u << DB) - 1;
     uint16_t *out = base + n;
     uint16_t *const lim = base + (cap > SYM_SLACK ? cap - SYM_SLACK : 0);
+    // ---- fast loop ------------------------------------------------------------------------------
+    {
+        const uint64_t bit0 = br.bitpos();
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(br.in);
+        uint64_t wi = bit0 >> 5;                                       // word that holds the next bit
+        const uint64_t wi_end = br.size >= 64 ? (br.size - 32) >> 2 : 0;   // stay clear of the end: the careful loop finishes
+        if (wi + 4 < wi_end) {
+            uint32_t off = (uint32_t)(bit0 & 31);
+            uint32_t lo = __ldg(wp + wi), hi = __ldg(wp + wi + 1), nx = __ldg(wp + wi + 2);
+            int rc = 1;                                                // 1: left the loop near the end of the input / output
+#define GI_NORMALISE() if (off >= 32) { lo = hi; hi = nx; wi++; nx = __ldg(wp + wi + 2); off -= 32; }
+            while (wi + 4 < wi_end && out < lim) {
+                uint32_t win = __funnelshift_r(lo, hi, off);
+                uint32_t e = T.lit[win & LMASK];
+                if ((e & 0x300) == 0) {                               // K_LIT or K_LIT2: one or two literals
+                    const uint32_t v = e >> 16;
+                    if (STRICT && !(texty(v & 0xff) && ((e & 0x400) == 0 || texty(v >> 8)))) { rc = D_REJECT; break; }
+                    out[0] = (uint16_t)(v & 0xff);
+                    out[1] = (uint16_t)(v >> 8);                      // overwritten by what follows unless this is a pair
+                    out += 1 + ((e >> 10) & 1);
+                    off += e & 15;
+                    GI_NORMALISE();
+                    continue;
+                }
+                uint32_t used = e_nbits(e);
+                if (e_kind(e) == K_LINK) {
+                    e = T.lit[e_val(e) + ((win >> LB) & ((1u << e_extra(e)) - 1))];
+                    used = LB + e_nbits(e);
+                }
+                const uint32_t kind = e_kind(e);
+                if (kind == K_LIT) {
+                    if (STRICT && !texty(e_val(e))) { rc = D_REJECT; break; }
+                    *out++ = (uint16_t)e_val(e);
+                    off += used;
+                    GI_NORMALISE();
+                    continue;
+                }
+                if (kind == K_BASE) {
+                    const uint32_t xl = e_extra(e);
+                    const uint32_t len = e_val(e) + ((win >> used) & ((1u << xl) - 1));
+                    off += used + xl;
+                    GI_NORMALISE();
+                    win = __funnelshift_r(lo, hi, off);
+                    uint32_t d = T.dist[win & DMASK];
+                    uint32_t du = e_nbits(d);
+                    if (e_kind(d) == K_LINK) {
+                        d = T.dist[e_val(d) + ((win >> DB) & ((1u << e_extra(d)) - 1))];
+                        du = DB + e_nbits(d);
+                    }
+                    if (e_kind(d) != K_BASE) { rc = STRICT ? D_REJECT : D_ERROR; break; }
+                    const uint32_t xd = e_extra(d);
+                    const uint32_t dist = e_val(d) + ((win >> du) & ((1u << xd) - 1));
+                    off += du + xd;
+                    GI_NORMALISE();
+                    copy_match(base, out, len, dist);
+                    out += len;
+                    continue;
+                }
+                if (kind == K_EOB) { off += used; rc = D_OK; break; }
+                rc = STRICT ? D_REJECT : D_ERROR;
+                break;
+            }
+#undef GI_NORMALISE
+            n = (uint32_t)(out - base);
+            if (rc < 0) return rc;
+            br.init(br.in, br.size, wi * 32 + off);                    // hand the position back to the careful reader
+            if (rc == D_OK) return br.overrun() ? (STRICT ? D_REJECT : D_ERROR) : D_OK;
+        }
+    }
+    // ---- careful loop: the end of the input, the end of the output buffer --------------------------
     for (;;) {
         if (out >= lim) { n = (uint32_t)(out - base); return D_OVERFLOW; }
         // a literal/length code needs at most 15 bits; the rest of a length/distance pair is topped up below

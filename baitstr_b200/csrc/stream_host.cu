@@ -297,6 +297,7 @@ struct Pipeline {
     int n_readers = 4;                    // host threads the caller allows (bstr_params.host_threads, at least 4)
     int plain_readers = 4;                // threads that read one plain file in parallel segments
     int gz_decoders = 4, gz_fillers = 2, gz_pending = 3;   // parallel inflate: decoder threads, segment producers, segments decoded ahead
+    std::vector<int> gz_active;           // .gz windows running per device (mu): a device takes another one only if no device has fewer
     bool gpu_inflate = true;              // "*.gz" files of some size go through the GPU inflater (BSTR_GPU_INFLATE=0: host threads)
     uint64_t gz_gpu_min = 8u << 20;       // ... from this compressed size on
     size_t gz_window = 0, gz_range = 0;   // its geometry (BSTR_GZ_WINDOW / BSTR_GZ_RANGE, bytes)
@@ -847,10 +848,15 @@ static void device_main(Pipeline *pp, int d)
                 for (int l = d; l < ctx->n_lanes; l += ndev) if (P.lane_state[l] == 0) { lane = l; break; }
                 if (lane >= 0 && !P.work.empty()) {
                     gz_slot = -1;
-                    if (P.work.front()->gz) for (int g = 0; g < GZ_PAR; g++) if (!gz_busy[g]) { gz_slot = g; break; }
+                    if (P.work.front()->gz) {
+                        int least = P.gz_active[(size_t)d];
+                        for (int o = 0; o < ndev; o++) if (P.gz_active[(size_t)o] < least) least = P.gz_active[(size_t)o];
+                        if (P.gz_active[(size_t)d] == least)      // spread the windows over the GPUs before doubling up on one
+                            for (int g = 0; g < GZ_PAR; g++) if (!gz_busy[g]) { gz_slot = g; break; }
+                    }
                     if (!P.work.front()->gz || gz_slot >= 0) {
                         job = P.work.front(); P.work.pop_front(); P.lane_state[lane] = 1;
-                        if (gz_slot >= 0) gz_busy[gz_slot] = true;
+                        if (gz_slot >= 0) { gz_busy[gz_slot] = true; P.gz_active[(size_t)d]++; P.cv_work.notify_all(); }   // the others look at the new front
                         break;
                     }
                 }
@@ -878,7 +884,7 @@ static void device_main(Pipeline *pp, int d)
                 const bool hold = job->rc == BSTR_OK && job->bo.out_bytes;
                 job->lane = hold ? lane : -1;
                 ctx->lanes[lane].busy = false;
-                { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = hold ? 2 : 0; gz_busy[gz_slot] = false; }
+                { std::lock_guard<std::mutex> g(P.mu); P.lane_state[lane] = hold ? 2 : 0; gz_busy[gz_slot] = false; P.gz_active[(size_t)d]--; }
                 publish(P, job);
                 P.cv_work.notify_all();
             });
@@ -959,6 +965,7 @@ extern "C" int bstr_run_files(bstr_ctx *ctx, const char *const *paths, int npath
     }
     P.bufs_max = (size_t)ctx->n_lanes + 2 + (size_t)(P.plain_readers > P.gz_fillers ? P.plain_readers : P.gz_fillers);
     P.lane_state.assign((size_t)ctx->n_lanes, 0);
+    P.gz_active.assign((size_t)ctx->p.n_devices, 0);
     for (auto &b : ctx->engine->pool) {
         if (b.cap == P.buf_cap && P.bufs_made < P.bufs_max) { P.free_bufs.push_back(b); P.bufs_made++; }
         else cudaFreeHost(b.p);
