@@ -3,6 +3,7 @@
 
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <zlib.h>                      // crc32_combine only
 
@@ -17,7 +18,7 @@ namespace ginflate {
 // crc(A) * x^(8 |B|) mod P  xor  crc(B) over GF(2), bit-reflected polynomial 0xEDB88320.  The operator
 // x^(8 n) mod P for the fixed chunk length is computed once.
 constexpr uint32_t CRC_CHUNK = 8u << 10;
-constexpr size_t TARGET_RANGES = 2800;          // ~ the warps a B200 holds for k_decode_ranges (148 SMs x 20)
+static size_t TARGET_RANGES = 2800;             // ~ the warps a B200 holds for k_decode_ranges (148 SMs x 20); BSTR_GZ_TARGET_RANGES
 constexpr size_t MIN_RANGE = 16u << 10;
 constexpr size_t SYM_EXTRA = 256u << 10;        // symbols a range may produce beyond 10x its size (the block that straddles its end)
 static uint32_t gf2_multmodp(uint32_t a, uint32_t b)
@@ -88,6 +89,7 @@ Device *Device::create(size_t window_bytes, size_t look_ahead, size_t range_byte
     if (range_bytes < 4096) range_bytes = 4096;
     if (window_bytes < range_bytes) window_bytes = range_bytes;
     p->window_bytes = window_bytes; p->look_ahead = look_ahead; p->range_bytes = range_bytes;
+    if (const char *tr = getenv("BSTR_GZ_TARGET_RANGES")) { if (atoll(tr) >= 64 && atoll(tr) <= 60000) TARGET_RANGES = (size_t)atoll(tr); }
     const size_t full = (window_bytes + range_bytes - 1) / range_bytes;         // ranges of a full window
     p->max_ranges = (int)(full > TARGET_RANGES + 256 ? full : TARGET_RANGES + 256); // a short window is cut into smaller ranges (decode)
     p->sym_cap = (uint32_t)(range_bytes * 10 + SYM_EXTRA);
