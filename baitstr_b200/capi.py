@@ -57,7 +57,8 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_match_reads", "bstr_bench_resident", "bstr_host_alloc", "bstr_host_free",
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
-           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu"]
+           "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu",
+           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy"]
 
 _lib = None
 
@@ -122,6 +123,16 @@ def load_library():
     lib.bstr_device_count.restype = C.c_int
     lib.bstr_gunzip.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
     lib.bstr_gunzip.restype = C.c_int
+    lib.bstr_kmers_create.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
+    lib.bstr_kmers_create.restype = C.c_void_p
+    lib.bstr_kmers_add_fastq.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.bstr_kmers_add_fastq.restype = C.c_int
+    lib.bstr_kmers_finish.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.bstr_kmers_finish.restype = C.c_int
+    lib.bstr_kmers_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    lib.bstr_kmers_stats.restype = None
+    lib.bstr_kmers_destroy.argtypes = [C.c_void_p]
+    lib.bstr_kmers_destroy.restype = None
     lib.bstr_gunzip_gpu.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
     lib.bstr_gunzip_gpu.restype = C.c_int
     _lib = lib
@@ -384,6 +395,33 @@ class Context:
         if rc:
             self._raise(rc)
         return ms.value
+
+    def count_kmers(self, batches, klen, min_threshold=2, max_threshold=255, expected_kmers=1 << 20):
+        """bstr_kmers_*: the k-mer counting pass of extend_STR_reads over raw FASTQ batches (whole
+        records each).  Returns (uint64 k-mers sorted, uint8 counts, stats dict)."""
+        h = self._lib.bstr_kmers_create(self._ctx, int(klen), int(expected_kmers))
+        if not h:
+            self._raise(-3)
+        try:
+            for b in batches:
+                addr, n, keep = self._addr(b)
+                rc = self._lib.bstr_kmers_add_fastq(h, addr, n)
+                if rc:
+                    self._raise(rc)
+            kp, cp, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
+            rc = self._lib.bstr_kmers_finish(h, int(min_threshold), int(max_threshold), C.byref(kp), C.byref(cp), C.byref(n))
+            if rc:
+                self._raise(rc)
+            if n.value:
+                kmers = np.ctypeslib.as_array((C.c_uint64 * n.value).from_address(kp.value)).copy()
+                counts = np.ctypeslib.as_array((C.c_uint8 * n.value).from_address(cp.value)).copy()
+            else:
+                kmers, counts = np.zeros(0, np.uint64), np.zeros(0, np.uint8)
+            st = (C.c_uint64 * 4)()
+            self._lib.bstr_kmers_stats(h, st)
+            return kmers, counts, dict(zip(("records", "kmers", "distinct", "slots"), [int(x) for x in st]))
+        finally:
+            self._lib.bstr_kmers_destroy(h)
 
     def stats(self):
         st = Stats()

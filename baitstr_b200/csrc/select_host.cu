@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <chrono>
 #include <mutex>
 #include <vector>
@@ -418,3 +419,4 @@ void bstr_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 #include "batch_api.inc"
 #include "noalloc_api.inc"
+#include "kmer_api.inc"

@@ -232,6 +232,28 @@ int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes,
 int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_t window_bytes, uint64_t range_bytes,
                     uint64_t *stats6, char *err, size_t errlen);
 
+/* First slice of the stage after next: the k-mer counting pass of
+ * extend_STR_reads on the GPU.  Replaces ReadAndCountNonSingletonKmers,
+ * /root/reference/src/extend_STR_reads.c:31-194 (Bloom filter of singletons + sparse hash map of
+ * canonical 2-bit k-mers, kmer.c:4-47, then the threshold pruning :187-193): every k-mer of every
+ * read is counted exactly in one pass in an open-addressing table in HBM, and bstr_kmers_finish returns
+ * { canonical k-mer : min(count, 255) } for min_threshold <= count <= max_threshold, sorted by k-mer.
+ * The k-mer arithmetic is the reference's bit for bit (uint64_t, klen in 2..31), including what a base
+ * outside ACGTacgt does to the rolling word (N and n read as A, anything else adds -1:
+ * utilities.h:61-75).  min_threshold must be >= 2: below that the reference's own result depends on
+ * its Bloom filter's false positives (seeded from time()).
+ *   create     expected_kmers = distinct k-mers the table must hold, singletons included
+ *   add_fastq  raw FASTQ in host memory: whole 4-line records, newline-terminated; any number of calls
+ *   finish     the arrays belong to the handle and stay valid until it is destroyed
+ *   stats      out4 = {records, k-mers counted, distinct k-mers, table slots} */
+typedef struct bstr_kmers bstr_kmers;
+bstr_kmers *bstr_kmers_create(bstr_ctx *ctx, int klen, uint64_t expected_kmers);
+int bstr_kmers_add_fastq(bstr_kmers *k, const uint8_t *raw, uint64_t nbytes);
+int bstr_kmers_finish(bstr_kmers *k, int min_threshold, int max_threshold, const uint64_t **kmers,
+                      const uint8_t **counts, uint64_t *n);
+void bstr_kmers_stats(const bstr_kmers *k, uint64_t out4[4]);
+void bstr_kmers_destroy(bstr_kmers *k);
+
 /* number of CUDA devices visible (0 if none / no driver) */
 int bstr_device_count(void);
 

@@ -23,5 +23,9 @@ V=$(cat "$REF/VERSION")
 for prog in merge_STR_reads extend_STR_reads; do
   g++ -O3 -w -D"VERSION=\"$V\"" -I"$B/sparse/src" -I"$REF/sparsehash/src" -I"$REF" -o "$B/$prog" $OBJS "$REF/$prog.c" -lz -lm
 done
+# the reference's k-mer counting pass alone (extend_STR_reads.c:31-194) behind a dump harness: the oracle
+# of the GPU k-mer counter (bstr_kmers_*)
+g++ -O3 -w -D"VERSION=\"$V\"" -Dmain=reference_extend_main -DREFERENCE_EXTEND_C="\"$REF/extend_STR_reads.c\"" \
+    -I"$B/sparse/src" -I"$REF/sparsehash/src" -I"$REF" -o "$B/kmer_count_ref" $OBJS "$HERE/kmer_ref_harness.cc" -lz -lm
 rm -f $OBJS
 echo "oracle/_ref/downstream: ok"
