@@ -58,7 +58,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
            "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu",
-           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy"]
+           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy", "bstr_merge_reads"]
 
 _lib = None
 
@@ -123,6 +123,8 @@ def load_library():
     lib.bstr_device_count.restype = C.c_int
     lib.bstr_gunzip.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
     lib.bstr_gunzip.restype = C.c_int
+    lib.bstr_merge_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+    lib.bstr_merge_reads.restype = C.c_int
     lib.bstr_kmers_create.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
     lib.bstr_kmers_create.restype = C.c_void_p
     lib.bstr_kmers_add_fastq.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
@@ -395,6 +397,20 @@ class Context:
         if rc:
             self._raise(rc)
         return ms.value
+
+    def merge_reads(self, fastq, klength, min_threshold=4, max_threshold=10000, include_all=False):
+        """bstr_merge_reads: the select stage's output -> (the blocks merge_STR_reads would print, stats dict)."""
+        import tempfile
+        addr, n, keep = self._addr(fastq)
+        st = (C.c_uint64 * 6)()
+        with tempfile.TemporaryFile() as f:
+            rc = self._lib.bstr_merge_reads(self._ctx, addr, n, int(klength), int(min_threshold), int(max_threshold),
+                                            int(bool(include_all)), f.fileno(), st)
+            if rc:
+                self._raise(rc)
+            f.seek(0)
+            out = f.read()
+        return out, dict(zip(("reads", "keys", "chains", "blocks", "printed", "longest_chain"), [int(x) for x in st]))
 
     def count_kmers(self, batches, klen, min_threshold=2, max_threshold=255, expected_kmers=1 << 20):
         """bstr_kmers_*: the k-mer counting pass of extend_STR_reads over raw FASTQ batches (whole

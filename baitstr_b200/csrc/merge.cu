@@ -1,0 +1,259 @@
+// merge.cu -- bstr_merge_reads: the merge stage (merge_STR_reads) on the GPU, first slice
+// (SURVEY.md 8(f) rank 2).  Replaces MergeShortTandemRepeatReads, /root/reference/src/merge_STR_reads.c:308-509.
+//
+// The reference runs one loop over the reads; a read meets earlier reads only through the map keyed
+// by "motif lflank rflank", looked up for the read as it is and reverse-complemented.  Reads whose
+// keys never touch cannot influence each other, so the reads are cut into CHAINS (connected
+// components over the two keys of every read, merge_plan.h) and every chain is walked in input
+// order by ONE WARP: the 32 lanes fill the two local-alignment matrices of AlignFlanks along
+// anti-diagonals, lane 0 walks the traceback and rewrites the block (merge_step.cuh, merge_core.cuh
+// -- the same source the CPU suite runs on the host).  Blocks live in HBM, one slot per key; the
+// two-bit traceback matrix, the three live anti-diagonals and the consensus flanks in shared memory.
+// Parsing, keys, chains, the reference's table order and printing are host work (merge_plan.h).
+#include <stdio.h>
+#include <stdlib.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <chrono>
+#include <numeric>
+
+#include "host_common.h"
+#include "merge_plan.h"
+#include "merge_step.cuh"
+
+namespace bmerge {
+
+constexpr int WARPS = 5;           // chains in flight per CTA: shared memory allows one CTA per SM
+
+struct WarpShared {
+    uint8_t T[T_BYTES];
+    int16_t diag[3][PITCH];
+    char cons[4][MAXB];
+};
+static_assert(sizeof(WarpShared) * WARPS <= 227 * 1024, "shared memory of one CTA");
+
+struct WarpExec {
+    int lane;
+    int16_t *d0, *d1, *d2;
+    // Align's matrix (:86-110) along anti-diagonals d = i + j: a cell needs (i, j-1) and (i-1, j) of
+    // diagonal d-1 and (i-1, j-1) of d-2, all indexed by their row here
+    __device__ __forceinline__ uint64_t dp_fill(const char *t1, int len1, const char *t2, int len2, uint8_t *T)
+    {
+        uint64_t best = 0;
+        int16_t *p2 = d0, *p1 = d1, *cur = d2;
+        if (len1 >= 2 && len2 >= 2) {
+            for (int d = 2; d <= len1 + len2 - 2; d++) {
+                const int ilo = max(1, d - (len2 - 1)), ihi = min(len1 - 1, d - 1);
+                for (int i = ilo + lane; i <= ihi; i += 32) {
+                    const int j = d - i;
+                    const int left = j >= 2 ? p1[i] : 0, up = i >= 2 ? p1[i - 1] : 0, dg = (i >= 2 && j >= 2) ? p2[i - 1] : 0;
+                    unsigned code;
+                    const int a = dp_cell(left, up, dg, t1[i - 1] == t2[j - 1], &code);
+                    cur[i] = (int16_t)a;
+                    t_put(T, i, j, code);            // cells of one diagonal lie PITCH - 1 apart: never in the same byte
+                    const uint64_t key = best_key(a, i, j);
+                    best = key > best ? key : best;
+                }
+                __syncwarp();
+                int16_t *t = p2; p2 = p1; p1 = cur; cur = t;
+            }
+        }
+        for (int o = 16; o; o >>= 1) {
+            const uint64_t other = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+            best = other > best ? other : best;
+        }
+        return best;
+    }
+    __device__ __forceinline__ bool leader() const { return lane == 0; }
+    __device__ __forceinline__ int bcast(int v) const { return __shfl_sync(0xFFFFFFFFu, v, 0); }
+    __device__ __forceinline__ void sync() const { __syncwarp(); }
+};
+
+// a warp per chain, chains handed out by a ticket (longest first: the host sorts them)
+__global__ void __launch_bounds__(WARPS * 32)
+k_merge_chains(const Read *reads, const uint32_t *chain_start, const uint32_t *chain_reads, const uint32_t *chain_order, uint32_t nchains,
+               BlockHead *heads, char *bseqs, char *bquals, const char *fwd, const char *qfwd, const char *rev, const char *qrev,
+               unsigned *ticket, int *err)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    WarpShared *w = reinterpret_cast<WarpShared *>(smem) + (threadIdx.x >> 5);
+    WarpExec x{(int)(threadIdx.x & 31), w->diag[0], w->diag[1], w->diag[2]};
+    const Scratch s{w->T, w->cons[0], w->cons[1], w->cons[2], w->cons[3]};
+    for (;;) {
+        unsigned t = 0;
+        if (x.lane == 0) t = atomicAdd(ticket, 1u);
+        t = __shfl_sync(0xFFFFFFFFu, t, 0);
+        if (t >= nchains) return;
+        const uint32_t c = chain_order[t];
+        for (uint32_t at = chain_start[c]; at < chain_start[c + 1]; at++) {
+            const uint32_t i = chain_reads[at];
+            const int e = process_read(x, reads[i], (int)i, heads, bseqs, bquals, fwd, qfwd, rev, qrev, s);
+            if (e) {                                   // the whole call fails: remember the first reason
+                if (x.lane == 0 && atomicCAS(&err[0], 0, e) == 0) err[1] = (int)i;
+                return;
+            }
+        }
+    }
+}
+
+__global__ void k_merge_init(BlockHead *heads, uint32_t nkeys)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nkeys) { BlockHead h; memset(&h, 0, sizeof h); h.created_by = -1; heads[k] = h; }
+}
+
+// the sequences of the blocks that will be printed, side by side
+__global__ void k_merge_gather(const uint32_t *which, uint32_t n, const char *bseqs, const char *bquals, char *oseq, char *oqual)
+{
+    const uint32_t b = blockIdx.x;
+    if (b >= n) return;
+    const size_t from = (size_t)which[b] * MAXB, to = (size_t)b * MAXB;
+    for (int a = threadIdx.x; a < MAXB; a += blockDim.x) { oseq[to + a] = bseqs[from + a]; oqual[to + a] = bquals[from + a]; }
+}
+
+static const char *err_text(int e)
+{
+    switch (e) {
+    case ERR_FLANK_TOO_LONG: return "a flank longer than 383 bases (the alignment matrix is held in shared memory)";
+    case ERR_BLOCK_TOO_LONG: return "a block longer than 799 bases";
+    case ERR_TOO_MANY_ALLELES: return "more than 24 different copy numbers in one block";
+    }
+    return "?";
+}
+
+}  // namespace bmerge
+
+using namespace bmerge;
+
+namespace {
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    template <class T> T *as() { return (T *)p; }
+};
+}
+
+extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nbytes, int klength, int min_threshold, int max_threshold,
+                                int include_all, int out_fd, uint64_t stats[6])
+{
+    using bstr::set_error;
+    using bstr::cuda_fail;
+    if (!ctx || (!fastq && nbytes)) return BSTR_ERR_PARAM;
+    if (klength < 1 || klength > 1000) { set_error(ctx, "bstr_merge_reads: klength %d", klength); return BSTR_ERR_PARAM; }
+    if (klength % 2 == 0) klength--;                                       // merge_STR_reads.c:557-560
+    if (include_all && min_threshold < 2) {
+        set_error(ctx, "bstr_merge_reads: --all with min_threshold < 2: the reference stops on its own assertion at the first unmerged block (merge_STR_reads.c:468)");
+        return BSTR_ERR_PARAM;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    Plan P;
+    if (!make_plan(fastq, nbytes, klength, P)) { set_error(ctx, "bstr_merge_reads: %s", P.error.c_str()); return BSTR_ERR_PARAM; }
+    const uint32_t nreads = (uint32_t)P.reads.size(), nkeys = (uint32_t)P.keys.size(), nchains = (uint32_t)P.chain_start.size() - 1;
+    std::string out;
+    uint64_t st_blocks = 0, st_printed = 0, st_longest = 0;
+    double ms_plan = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), ms_dev = 0, ms_kernel = 0;
+    if (nreads) {
+        // longest chains first
+        std::vector<uint32_t> order(nchains);
+        std::iota(order.begin(), order.end(), 0u);
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+            return P.chain_start[a + 1] - P.chain_start[a] > P.chain_start[b + 1] - P.chain_start[b];
+        });
+        st_longest = P.chain_start[order[0] + 1] - P.chain_start[order[0]];
+        const auto t1 = std::chrono::steady_clock::now();
+        CUDA_TRY(cudaSetDevice(ctx->dev));
+        cudaStream_t st = ctx->stream;
+        DevBuf d_reads, d_cs, d_cr, d_co, d_heads, d_bseq, d_bqual, d_fwd, d_qfwd, d_rev, d_qrev, d_misc, d_which, d_oseq, d_oqual;
+        const size_t blob = P.fwd.size();
+#define BM_UP(buf, src, bytes)                                                                                     \
+        do {                                                                                                           \
+            if (cudaMalloc(&buf.p, (bytes) ? (bytes) : 1) != cudaSuccess) return cuda_fail(ctx, cudaGetLastError(), "merge: cudaMalloc", __LINE__); \
+            if ((src) && (bytes)) CUDA_TRY(cudaMemcpyAsync(buf.p, (src), (bytes), cudaMemcpyHostToDevice, st));          \
+        } while (0)
+        BM_UP(d_reads, P.reads.data(), (size_t)nreads * sizeof(Read));
+        BM_UP(d_cs, P.chain_start.data(), (size_t)(nchains + 1) * 4);
+        BM_UP(d_cr, P.chain_reads.data(), (size_t)nreads * 4);
+        BM_UP(d_co, order.data(), (size_t)nchains * 4);
+        BM_UP(d_fwd, P.fwd.data(), blob);
+        BM_UP(d_qfwd, P.qfwd.data(), blob);
+        BM_UP(d_rev, P.rev.data(), blob);
+        BM_UP(d_qrev, P.qrev.data(), blob);
+        BM_UP(d_heads, (const void *)nullptr, (size_t)nkeys * sizeof(BlockHead));
+        BM_UP(d_bseq, (const void *)nullptr, (size_t)nkeys * MAXB);
+        BM_UP(d_bqual, (const void *)nullptr, (size_t)nkeys * MAXB);
+        BM_UP(d_misc, (const void *)nullptr, 16);
+        CUDA_TRY(cudaMemsetAsync(d_misc.p, 0, 16, st));
+        k_merge_init<<<(nkeys + 255) / 256, 256, 0, st>>>(d_heads.as<BlockHead>(), nkeys);
+        const size_t smem = sizeof(WarpShared) * WARPS;
+        CUDA_TRY(cudaFuncSetAttribute(k_merge_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaEvent_t e0, e1;
+        CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+        const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, ((uint64_t)nchains + WARPS - 1) / WARPS);
+        cudaEventRecord(e0, st);
+        k_merge_chains<<<grid, WARPS * 32, smem, st>>>(d_reads.as<Read>(), d_cs.as<uint32_t>(), d_cr.as<uint32_t>(), d_co.as<uint32_t>(), nchains,
+                                                        d_heads.as<BlockHead>(), d_bseq.as<char>(), d_bqual.as<char>(), d_fwd.as<char>(),
+                                                        d_qfwd.as<char>(), d_rev.as<char>(), d_qrev.as<char>(), d_misc.as<unsigned>(),
+                                                        d_misc.as<int>() + 1);
+        cudaEventRecord(e1, st);
+        cudaError_t le = cudaGetLastError();
+        if (le != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return cuda_fail(ctx, le, "k_merge_chains", __LINE__); }
+        std::vector<BlockHead> heads(nkeys);
+        int misc[4] = {0, 0, 0, 0};
+        cudaError_t ce = cudaMemcpyAsync(heads.data(), d_heads.p, (size_t)nkeys * sizeof(BlockHead), cudaMemcpyDeviceToHost, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(misc, d_misc.p, 16, cudaMemcpyDeviceToHost, st);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+        float kms = 0;
+        if (ce == cudaSuccess) cudaEventElapsedTime(&kms, e0, e1);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        if (ce != cudaSuccess) return cuda_fail(ctx, ce, "merge: kernel / download", __LINE__);
+        ms_kernel = kms;
+        if (misc[1]) {
+            set_error(ctx, "bstr_merge_reads: read %d: %s", misc[2] + 1, err_text(misc[1]));
+            return BSTR_ERR_TOO_LARGE;
+        }
+        // the keys in the order their blocks entered the reference's map = the order of the reads that made them
+        std::vector<std::pair<int32_t, uint32_t>> made;
+        for (uint32_t k = 0; k < nkeys; k++) if (heads[k].created_by >= 0) made.push_back({heads[k].created_by, k});
+        std::sort(made.begin(), made.end());
+        std::vector<uint32_t> inserted(made.size());
+        for (size_t i = 0; i < made.size(); i++) inserted[i] = made[i].second;
+        st_blocks = inserted.size();
+        const std::vector<uint32_t> listed = table_order(P.keys, inserted);
+        std::vector<uint32_t> which;
+        for (uint32_t k : listed)
+            if (block_verdict(heads[k], (unsigned)min_threshold, (unsigned)max_threshold, include_all != 0).print) which.push_back(k);
+        st_printed = which.size();
+        std::vector<char> oseq(which.size() * (size_t)MAXB), oqual(which.size() * (size_t)MAXB);
+        if (!which.empty()) {
+            BM_UP(d_which, which.data(), which.size() * 4);
+            BM_UP(d_oseq, (const void *)nullptr, oseq.size());
+            BM_UP(d_oqual, (const void *)nullptr, oqual.size());
+            k_merge_gather<<<(unsigned)which.size(), 128, 0, st>>>(d_which.as<uint32_t>(), (uint32_t)which.size(), d_bseq.as<char>(), d_bqual.as<char>(),
+                                                                  d_oseq.as<char>(), d_oqual.as<char>());
+            CUDA_TRY(cudaGetLastError());
+            CUDA_TRY(cudaMemcpyAsync(oseq.data(), d_oseq.p, oseq.size(), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(oqual.data(), d_oqual.p, oqual.size(), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+        }
+#undef BM_UP
+        unsigned bindex = 1;
+        for (size_t b = 0; b < which.size(); b++)
+            print_block(out, bindex, P.keys[which[b]], heads[which[b]], &oseq[b * (size_t)MAXB], &oqual[b * (size_t)MAXB], (unsigned)min_threshold,
+                        (unsigned)max_threshold, include_all != 0);
+        ms_dev = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+    }
+    if (out_fd >= 0) {
+        size_t done = 0;
+        while (done < out.size()) {
+            const ssize_t n = write(out_fd, out.data() + done, out.size() - done);
+            if (n <= 0) { set_error(ctx, "bstr_merge_reads: write failed"); return BSTR_ERR_IO; }
+            done += (size_t)n;
+        }
+    }
+    if (stats) { stats[0] = nreads; stats[1] = nkeys; stats[2] = nchains; stats[3] = st_blocks; stats[4] = st_printed; stats[5] = st_longest; }
+    if (getenv("BSTR_TRACE"))
+        fprintf(stderr, "[bstr_merge] %u reads, %u keys, %u chains (longest %llu), %llu blocks, %llu printed: plan %.1f ms, device part %.1f ms (kernel %.2f ms)\n",
+                nreads, nkeys, nchains, (unsigned long long)st_longest, (unsigned long long)st_blocks, (unsigned long long)st_printed, ms_plan, ms_dev, ms_kernel);
+    return BSTR_OK;
+}

@@ -232,6 +232,24 @@ int bstr_gunzip(const char *path, int out_fd, int threads, uint64_t range_bytes,
 int bstr_gunzip_gpu(const char *path, int out_fd, int device, uint64_t window_bytes, uint64_t range_bytes,
                     uint64_t *stats6, char *err, size_t errlen);
 
+/* First slice of the next stage: merge_STR_reads on the GPU.  Replaces
+ * MergeShortTandemRepeatReads, /root/reference/src/merge_STR_reads.c:308-509 (with Align :43-213 and
+ * AlignFlanks :215-306): `fastq` is the select stage's output (annotated names), the polymorphic
+ * blocks are written to out_fd byte for byte as `merge_STR_reads [--min_threshold=..]
+ * [--max_threshold=..] [--all] klength reads.str.fq` prints them -- same blocks, same consensus
+ * sequences and qualities, same order and numbering (the order is that of the reference's hash map,
+ * replayed).  The reads are cut into chains that cannot influence each other and a warp walks each
+ * chain; the local alignments run on the 32 lanes.
+ *   klength        as the reference's: an even value is lowered by one (:557-560)
+ *   min_threshold / max_threshold / include_all   the options of the same names (defaults 4, 10000, 0)
+ *   out_fd         file descriptor for the blocks, < 0 = none
+ *   stats          NULL or {reads, keys, chains, blocks, blocks printed, longest chain}
+ * Refused with an error instead of reproducing undefined behaviour of the reference: a flank shorter
+ * than klength (it reads outside the read), --all with min_threshold < 2 (its assertion :468 stops
+ * it), flanks > 383 or blocks > 799 bases. */
+int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nbytes, int klength, int min_threshold,
+                     int max_threshold, int include_all, int out_fd, uint64_t stats[6]);
+
 /* First slice of the stage after next: the k-mer counting pass of
  * extend_STR_reads on the GPU.  Replaces ReadAndCountNonSingletonKmers,
  * /root/reference/src/extend_STR_reads.c:31-194 (Bloom filter of singletons + sparse hash map of

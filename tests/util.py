@@ -102,3 +102,52 @@ def synth_fastq(nreads, L, seed, p_str=0.30, p_n=0.02, p_lower=0.01, tag="t", va
         q = "".join(chr(rng.randint(35, 73)) for _ in range(ll))
         out.append("@%s.%010d/1\n%s\n+\n%s\n" % (tag, idx, s, q))
     return "".join(out).encode("latin-1")
+
+
+def str_locus_reads(nloci, coverage, L, seed, err=0.01, indel=0.002, ctx=260, shared_flank=0.0):
+    """Reads (both strands, substitution and indel errors, mixed qualities) from `nloci` STR loci
+    with two alleles each: the input the merge stage sees after the select stage.  With
+    shared_flank > 0 some loci reuse another locus's left context (reads of different loci then
+    share keys: chains with several blocks)."""
+    rng = random.Random(seed)
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A"}
+    out = []
+    contexts = []
+    idx = 0
+    for locus in range(nloci):
+        k = rng.randint(2, 6)
+        while True:
+            motif = "".join(rng.choice("ACGT") for _ in range(k))
+            if len(set(motif)) > 1:
+                break
+        left = "".join(rng.choice("ACGT") for _ in range(ctx))
+        right = "".join(rng.choice("ACGT") for _ in range(ctx))
+        if contexts and rng.random() < shared_flank:
+            left = rng.choice(contexts)
+        contexts.append(left)
+        c1 = rng.randint(4, 12)
+        alleles = [c1, c1 if rng.random() < 0.3 else max(3, c1 + rng.choice([-3, -2, -1, 1, 2, 3]))]
+        for _ in range(coverage):
+            hap = left + motif * rng.choice(alleles) + right
+            start = rng.randint(0, len(hap) - L)
+            s = list(hap[start:start + L + 4])
+            i = 0
+            while i < len(s):
+                u = rng.random()
+                if u < err:
+                    s[i] = rng.choice([b for b in "ACGT" if b != s[i]])
+                elif u < err + indel:
+                    if rng.random() < 0.5:
+                        del s[i]
+                        continue
+                    s.insert(i, rng.choice("ACGT"))
+                    i += 1
+                i += 1
+            s = "".join(s[:L])
+            if rng.random() < 0.5:
+                s = "".join(comp[b] for b in reversed(s))
+            q = "".join(chr(rng.choice([35, 40, 50, 53, 54, 60, 70, 72, 73])) if rng.random() < 0.2 else "I" for _ in range(len(s)))
+            out.append("@m.%08d/1\n%s\n+\n%s\n" % (idx, s, q))
+            idx += 1
+    rng.shuffle(out)
+    return "".join(out).encode("latin-1")
