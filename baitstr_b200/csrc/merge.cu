@@ -239,7 +239,7 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
 #undef BM_UP
         unsigned bindex = 1;
         for (size_t b = 0; b < which.size(); b++)
-            print_block(out, bindex, P.keys[which[b]], heads[which[b]], &oseq[b * (size_t)MAXB], &oqual[b * (size_t)MAXB], (unsigned)min_threshold,
+            print_block(out, bindex, P.keys.key(which[b]), heads[which[b]], &oseq[b * (size_t)MAXB], &oqual[b * (size_t)MAXB], (unsigned)min_threshold,
                         (unsigned)max_threshold, include_all != 0);
         ms_dev = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
     }

@@ -25,26 +25,72 @@
 
 namespace bmerge {
 
+
+inline const unsigned char *complement_table()
+{   // the IUPAC complement in either case, a blank for everything else (the table of fastq_seq.c:146-150)
+    static unsigned char table[256];
+    static const bool made = [] {
+        static const char pairs[] = "ATCGBVDHKMRYNNSSWWXX";
+        for (int c = 0; c < 256; c++) table[c] = ' ';
+        for (int i = 0; pairs[i]; i += 2) {
+            const unsigned char a = (unsigned char)pairs[i], b = (unsigned char)pairs[i + 1];
+            table[a] = b; table[b] = a; table[a | 0x20] = (unsigned char)(b | 0x20); table[b | 0x20] = (unsigned char)(a | 0x20);
+        }
+        return true;
+    }();
+    (void)made;
+    return table;
+}
+inline unsigned char complement_of(unsigned char c) { return complement_table()[c]; }
+
+// the distinct keys of a run, numbered in order of first sight: open addressing over one arena of
+// key bytes (a std::unordered_map<std::string, ...> costs an allocation per key)
+struct KeyTable {
+    std::string arena;                          // key bytes back to back
+    std::vector<uint32_t> start, len;           // per key id
+    std::vector<uint64_t> hash;                 // per key id: the hash the table order needs anyway
+    std::vector<uint32_t> slot;                 // id + 1, 0 = empty
+    uint64_t mask = 0;
+    static uint64_t hash_of(const char *p, size_t n);
+    uint32_t intern(const char *p, size_t n)
+    {
+        if ((start.size() + 1) * 2 > slot.size()) grow();
+        const uint64_t h = hash_of(p, n);
+        for (uint64_t at = h & mask;; at = (at + 1) & mask) {
+            const uint32_t id1 = slot[at];
+            if (!id1) {
+                const uint32_t id = (uint32_t)start.size();
+                start.push_back((uint32_t)arena.size()); len.push_back((uint32_t)n); hash.push_back(h);
+                arena.append(p, n);
+                slot[at] = id + 1;
+                return id;
+            }
+            const uint32_t id = id1 - 1;
+            if (hash[id] == h && len[id] == n && memcmp(arena.data() + start[id], p, n) == 0) return id;
+        }
+    }
+    void grow()
+    {
+        const size_t n = slot.empty() ? 1024 : slot.size() * 2;
+        slot.assign(n, 0); mask = n - 1;
+        for (uint32_t id = 0; id < start.size(); id++) {
+            uint64_t at = hash[id] & mask;
+            while (slot[at]) at = (at + 1) & mask;
+            slot[at] = id + 1;
+        }
+    }
+    std::string key(uint32_t id) const { return arena.substr(start[id], len[id]); }
+    size_t size() const { return start.size(); }
+};
+
 struct Plan {
     std::vector<Read> reads;
     std::string fwd, rev, qfwd, qrev;           // blobs: bases / qualities, as read and reversed(-complemented)
-    std::vector<std::string> keys;              // key id -> "motif lflank rflank"
+    KeyTable keys;                              // key id -> "motif lflank rflank"
     std::vector<uint32_t> chain_start;          // chains (components): reads of chain c = chain_reads[chain_start[c] .. chain_start[c+1])
     std::vector<uint32_t> chain_reads;          // in input order within a chain
     std::string error;
 };
-
-inline unsigned char complement_of(unsigned char c)
-{   // the IUPAC complement in either case, a blank for everything else (the table of fastq_seq.c:146-150)
-    static const char pairs[] = "ATCGBVDHKMRYNNSSWWXX";
-    const unsigned char u = (unsigned char)(c & 0xDF), low = (unsigned char)(c & 0x20);
-    if (c < 64 || c > 127) return ' ';
-    for (int i = 0; pairs[i]; i += 2) {
-        if (u == (unsigned char)pairs[i]) return (unsigned char)(pairs[i + 1] | low);
-        if (u == (unsigned char)pairs[i + 1]) return (unsigned char)(pairs[i] | low);
-    }
-    return ' ';
-}
 
 inline bool parse_name(const char *s, const char *e, Read &r)
 {   // "%[^\t]\t%s\t%d\t%d\t%d\t%s\t%d\t%d\t%d" (:350-355)
@@ -76,16 +122,10 @@ inline bool parse_name(const char *s, const char *e, Read &r)
 inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P)
 {
     char msg[256];
-    std::unordered_map<std::string, uint32_t> key_ids;
-    auto key_id = [&](const std::string &k) {
-        auto it = key_ids.find(k);
-        if (it != key_ids.end()) return it->second;
-        const uint32_t id = (uint32_t)P.keys.size();
-        key_ids.emplace(k, id); P.keys.push_back(k);
-        return id;
-    };
     const char *p = (const char *)raw, *end = p + nbytes;
     uint64_t recno = 0;
+    P.fwd.reserve(nbytes / 2); P.qfwd.reserve(nbytes / 2); P.rev.reserve(nbytes / 2); P.qrev.reserve(nbytes / 2);
+    P.reads.reserve(nbytes / 256);
     auto line = [&](const char *&s, const char *&e) {
         if (p >= end) return false;
         s = p;
@@ -119,21 +159,27 @@ inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P)
         P.fwd.append(bs, L); P.fwd.push_back('\0');
         P.qfwd.append(qs, L); P.qfwd.push_back('\0');
         P.rev.resize(P.fwd.size()); P.qrev.resize(P.fwd.size());
-        for (size_t i = 0; i < L; i++) {
-            P.rev[r.off + i] = (char)complement_of((unsigned char)bs[L - 1 - i]);
-            P.qrev[r.off + i] = qs[L - 1 - i];
+        {
+            const unsigned char *comp = complement_table();
+            char *rv = &P.rev[r.off], *qv = &P.qrev[r.off];
+            for (size_t i = 0; i < L; i++) { rv[i] = (char)comp[(unsigned char)bs[L - 1 - i]]; qv[i] = qs[L - 1 - i]; }
+            rv[L] = 0; qv[L] = 0;
         }
-        P.rev[r.off + L] = 0; P.qrev[r.off + L] = 0;
         const int k = klength;
         if (r.fzstart < k || r.fend + k > (int)L || r.rzstart < k || r.rend + k > (int)L || r.fend < r.fzstart || r.rend < r.rzstart) {
             snprintf(msg, sizeof msg, "merge: record %llu: a flank is shorter than klength %d (the reference reads outside the read there)", (unsigned long long)recno, k);
             P.error = msg; return false;
         }
-        std::string key;
-        key.assign(r.fmotif).append(" ").append(P.fwd, r.off + r.fzstart - k, k).append(" ").append(P.fwd, r.off + r.fend, k);
-        r.fkey = key_id(key);
-        key.assign(r.rmotif).append(" ").append(P.rev, r.off + r.rzstart - k, k).append(" ").append(P.rev, r.off + r.rend, k);
-        r.rkey = key_id(key);
+        char key[8 + 2 * 1000 + 4];
+        auto make_key = [&](const char *motif, int mlen, const char *bases, int zstart, int end_) {
+            char *q = key;
+            memcpy(q, motif, (size_t)mlen); q += mlen; *q++ = ' ';
+            memcpy(q, bases + zstart - k, (size_t)k); q += k; *q++ = ' ';
+            memcpy(q, bases + end_, (size_t)k); q += k;
+            return (size_t)(q - key);
+        };
+        r.fkey = P.keys.intern(key, make_key(r.fmotif, r.fmlen, P.fwd.data() + r.off, r.fzstart, r.fend));
+        r.rkey = P.keys.intern(key, make_key(r.rmotif, r.rmlen, P.rev.data() + r.off, r.rzstart, r.rend));
         P.reads.push_back(r);
     }
     // chains: union-find over key ids, a read joins its two keys
@@ -198,12 +244,14 @@ inline uint64_t murmur3_x64_128_low(const void *data, size_t len)
 }
 
 // key ids in the order the reference's table would list them, given the order they were inserted in
-inline std::vector<uint32_t> table_order(const std::vector<std::string> &keys, const std::vector<uint32_t> &inserted)
+inline uint64_t KeyTable::hash_of(const char *p, size_t n) { return murmur3_x64_128_low(p, n); }
+
+inline std::vector<uint32_t> table_order(const KeyTable &keys, const std::vector<uint32_t> &inserted)
 {
     std::vector<uint64_t> hash(inserted.size());
     // the map's key type is a pointer (const char *): sparsehash drops the "known-0" low bits of the
     // hash of a pointer key, hash / sizeof(void *) (hashtable-common.h:351-361)
-    for (size_t i = 0; i < inserted.size(); i++) hash[i] = murmur3_x64_128_low(keys[inserted[i]].data(), keys[inserted[i]].size()) / 8;
+    for (size_t i = 0; i < inserted.size(); i++) hash[i] = keys.hash[inserted[i]] / 8;
     std::vector<int64_t> bucket(32, -1);        // index into `inserted`
     size_t n = 0;
     auto threshold = [](size_t buckets) { return (size_t)(buckets * 0.8f); };

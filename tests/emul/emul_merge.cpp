@@ -79,7 +79,7 @@ int main(int argc, char **argv)
     std::string out;
     unsigned bindex = 1;
     for (uint32_t k : table_order(P.keys, inserted))
-        print_block(out, bindex, P.keys[k], heads[k], &bseqs[(size_t)k * MAXB], &bquals[(size_t)k * MAXB], (unsigned)atoi(argv[2]),
+        print_block(out, bindex, P.keys.key(k), heads[k], &bseqs[(size_t)k * MAXB], &bquals[(size_t)k * MAXB], (unsigned)atoi(argv[2]),
                     (unsigned)atoi(argv[3]), atoi(argv[4]) != 0);
     fwrite(out.data(), 1, out.size(), stdout);
     fprintf(stderr, "%zu reads, %zu keys, %zu chains, %zu blocks\n", P.reads.size(), P.keys.size(), P.chain_start.size() - 1, inserted.size());
