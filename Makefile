@@ -4,8 +4,8 @@
 #                   (/root/reference/Makefile:4-11): select_STR_reads (driver script), VERSION,
 #                   select_STR_reads.so and fastq.so (extension modules under the reference's module
 #                   names), plus libbaitstr_select.so (C ABI + embedded sm_100a code) and the
-#                   Python package with the -c / -d diagnostics.  merge_STR_reads and
-#                   extend_STR_reads are the reference's own binaries and are not built here.
+#                   Python package with the -c / -d diagnostics; merge_STR_reads (the reference's
+#                   command line over bstr_merge_reads).  extend_STR_reads is not built here.
 PREFIX ?= bin
 PYTHON ?= python3
 
@@ -14,7 +14,7 @@ all:
 
 install: all
 	mkdir -p $(PREFIX)/baitstr_b200
-	[ "$(abspath $(PREFIX))" = "$(abspath bin)" ] || cp bin/select_STR_reads bin/VERSION $(PREFIX)/
+	[ "$(abspath $(PREFIX))" = "$(abspath bin)" ] || cp bin/select_STR_reads bin/merge_STR_reads bin/VERSION $(PREFIX)/
 	cp baitstr_b200/libbaitstr_select.so $(PREFIX)/
 	cp baitstr_b200/*.py $(PREFIX)/baitstr_b200/
 	$(PYTHON) baitstr_b200/ext/build_ext.py $(PREFIX) $(PREFIX)

@@ -512,6 +512,10 @@ def run_ours(args):
     if D.world == 1 and not args.no_ingest:
         ingest = measure_ingest(args.workload, args.ingest_reads, D.local)
 
+    nxt = None
+    if D.world == 1 and not args.no_other and not args.quick:
+        nxt = next_stages(D.local)
+
     line = {
         "metric": METRIC, "value": round(main["value"], 1), "unit": "reads/s", "n_gpus": D.world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(main["ms_step"], 4),
@@ -527,13 +531,79 @@ def run_ours(args):
         "gpu_launches": main["launches_per_step"] * args.steps,
         "roofline": main["roofline"], "cpu_baseline": cpu, "clocks": main["clocks"],
         "c3": c3, "other_configs": others or None, "multi_gpu": multi, "parity_vs_reference": parity_ref,
-        "ingest": ingest, "out_checksum_fnv1a": "%016x" % main["checksum"],
+        "ingest": ingest, "next_stages": nxt, "out_checksum_fnv1a": "%016x" % main["checksum"],
     }
     print(json.dumps(line))
     D.close()
     if multi is not None and multi.get("parity") != "byte-identical":
         print("bench.py: multi-GPU parity failed: %s" % json.dumps(multi), file=sys.stderr)
         sys.exit(1)
+
+
+def next_stages(device):
+    """SURVEY 8(f) ranks 2 and 3, the first slices of the stages after the path: the merge stage
+    (bstr_merge_reads) and the k-mer counting pass of extend_STR_reads (bstr_kmers_*), each timed on a
+    small synthetic input through the C ABI with host buffers, beside the reference's own code
+    (oracle/_ref/downstream: its sources compiled in place) with a cmp of the results."""
+    from baitstr_b200 import capi
+    from tests import util
+    down = os.path.join(ROOT, "oracle", "_ref", "downstream")
+    tmp = tempfile.mkdtemp(prefix="bstr_next_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    out = {}
+    try:
+        with capi.Context(devices=[device]) as ctx:
+            # merge: 2000 STR loci x 40 reads of 150 bp -> select (GPU) -> merge
+            raw = b"".join(util.str_locus_reads(500, 40, 150, seed=200 + i).replace(b"@m.", b"@m%d." % i) for i in range(4))
+            sel = ctx.scan_batch(raw)[0]
+            nsel = sel.count(b"\n") // 4
+            ctx.merge_reads(sel, 27)
+            best = 1e9
+            for _ in range(3):
+                t0 = time.perf_counter()
+                got, st = ctx.merge_reads(sel, 27)
+                best = min(best, time.perf_counter() - t0)
+            m = {"reads": nsel, "klength": 27, "chains": st["chains"], "blocks_printed": st["printed"], "reads_per_s": round(nsel / best, 1),
+                 "ms": round(best * 1e3, 2), "reference_reads_per_s": None, "identical_to_reference": None}
+            exe = os.path.join(down, "merge_STR_reads")
+            if os.path.exists(exe):
+                p = os.path.join(tmp, "sel.fq")
+                with open(p, "wb") as f:
+                    f.write(sel)
+                t0 = time.perf_counter()
+                want = subprocess.run([exe, "27", p], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout
+                m["reference_reads_per_s"] = round(nsel / (time.perf_counter() - t0), 1)
+                m["identical_to_reference"] = want == got
+            out["merge_STR_reads"] = m
+            # k-mer counting: 100 k reads of 150 bp from one 1 Mb genome, k = 27
+            raw = util.genome_reads(100000, 150, 1000000, seed=9)
+            expected = 100000 * 124 // 2 + 1000000
+            ctx.count_kmers([raw[: len(raw) // 20]], 27, expected_kmers=expected // 10)
+            best = 1e9
+            for _ in range(3):
+                t0 = time.perf_counter()
+                kmers, counts, st = ctx.count_kmers([raw], 27, expected_kmers=expected)
+                best = min(best, time.perf_counter() - t0)
+            k = {"reads": 100000, "k": 27, "kmers": st["kmers"], "kept": int(len(kmers)), "reads_per_s": round(100000 / best, 1),
+                 "kmers_per_s": round(st["kmers"] / best, 1), "ms": round(best * 1e3, 2), "reference_reads_per_s": None,
+                 "identical_to_reference": None}
+            exe = os.path.join(down, "kmer_count_ref")
+            if os.path.exists(exe):
+                p = os.path.join(tmp, "reads.fq")
+                with open(p, "wb") as f:
+                    f.write(raw)
+                t0 = time.perf_counter()
+                ref = subprocess.run([exe, "27", "2", "255", str(expected), p], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout
+                k["reference_reads_per_s"] = round(100000 / (time.perf_counter() - t0), 1)
+                want = [tuple(int(x) for x in ln.split()) for ln in ref.decode().splitlines()]
+                k["identical_to_reference"] = want == list(zip(kmers.tolist(), counts.tolist()))
+            out["extend_STR_reads_kmer_count"] = k
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    for name, v in out.items():
+        if v["identical_to_reference"] is False:
+            print("bench.py: %s differs from the reference" % name, file=sys.stderr)
+            sys.exit(1)
+    return out
 
 
 def measure_ingest(name, nreads, device):

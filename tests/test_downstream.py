@@ -64,7 +64,7 @@ def test_make_install_layout(tmp_path):
     prefix = str(tmp_path / "bin")
     subprocess.check_call(["make", "-s", "-C", ROOT, "install", "PREFIX=" + prefix], stdout=subprocess.DEVNULL)
     have = set(os.listdir(prefix))
-    assert {"select_STR_reads", "VERSION", "select_STR_reads.so", "fastq.so", "libbaitstr_select.so", "baitstr_b200"} <= have
+    assert {"select_STR_reads", "merge_STR_reads", "VERSION", "select_STR_reads.so", "fastq.so", "libbaitstr_select.so", "baitstr_b200"} <= have
     code = ("import sys; sys.path.insert(0, %r)\n"
             "from select_STR_reads import *\n"                      # /root/reference/src/select_STR_reads:61
             "import select_STR_reads as m, fastq\n"
@@ -120,3 +120,24 @@ def test_gpu_select_feeds_reference_merge_and_extend(tmp_path):
         assert r.stdout == util.gz_read("testdata_readme.out.gz")       # and byte-identical to the reference's select
         return r.stdout
     _check(*_pipeline(tmp_path, selected))
+
+
+@pytest.mark.gpu
+def test_gpu_select_and_merge_feed_reference_extend(tmp_path):
+    """README.md:265-287 with BOTH first stages from this repository: bin/select_STR_reads | bin/merge_STR_reads 27,
+    then the reference's extend_STR_reads -- the same block and the same contig."""
+    _, extend = _downstream()
+    reads = []
+    for i in (1, 2):
+        p = tmp_path / ("Illumina_100_500_%d.fq" % i)
+        p.write_bytes(util.gz_read("testdata_%d.fq.gz" % i))
+        reads.append(str(p))
+    sel = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "select_STR_reads"), "-i", "-n", "3", "-f", "29"] + reads,
+                         capture_output=True, check=True).stdout
+    (tmp_path / "reads.str.fq").write_bytes(sel)
+    merged = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "merge_STR_reads"), "27", str(tmp_path / "reads.str.fq")],
+                            capture_output=True, check=True).stdout
+    (tmp_path / "merged.reads.str.fq").write_bytes(merged)
+    contigs = subprocess.run([extend, "4000", "20", "27", str(tmp_path / "merged.reads.str.fq")] + reads, capture_output=True,
+                             check=True).stdout
+    _check(merged.decode().splitlines(), contigs.decode().splitlines())

@@ -18,6 +18,7 @@ import pytest
 
 from oracle import kmer_count
 from tests import util
+from tests.util import genome_reads
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "downstream", "kmer_count_ref")
@@ -47,28 +48,6 @@ def random_reads(n, lo, hi, alphabet, seed, tag=b"v"):
         ln = rng.randint(lo, hi)
         out.append(b"@%s%d\n%s\n+\n%s\n" % (tag, i, "".join(rng.choice(alphabet) for _ in range(ln)).encode(), b"I" * ln))
     return b"".join(out)
-
-
-def genome_reads(nreads, L, genome_len, seed, err=0.01):
-    """reads of both strands from one random genome with substitution errors: real coverage, so
-    most k-mers repeat (what extend_STR_reads is run on), the erroneous ones stay singletons"""
-    rng = np.random.default_rng(seed)
-    genome = rng.integers(0, 4, genome_len, dtype=np.uint8)
-    starts = rng.integers(0, genome_len - L, nreads)
-    codes = genome[starts[:, None] + np.arange(L)[None, :]]
-    flip = rng.random(nreads) < 0.5
-    codes[flip] = 3 - codes[flip][:, ::-1]
-    hit = rng.random(codes.shape) < err
-    codes[hit] = (codes[hit] + rng.integers(1, 4, int(hit.sum()), dtype=np.uint8)) & 3
-    bases = np.frombuffer(b"ACGT", np.uint8)[codes]
-    rec = np.empty((nreads, 12 + L + 3 + L + 1), np.uint8)
-    names = np.array([list(b"@g%09d\n" % i) for i in range(nreads)], np.uint8)
-    rec[:, :12] = names
-    rec[:, 12:12 + L] = bases
-    rec[:, 12 + L:12 + L + 3] = np.frombuffer(b"\n+\n", np.uint8)
-    rec[:, 12 + L + 3:12 + 2 * L + 3] = ord("I")
-    rec[:, -1] = 10
-    return rec.tobytes()
 
 
 CASES = [

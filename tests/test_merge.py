@@ -184,3 +184,49 @@ def test_gpu_errors_are_loud(capi):
         assert "parsing read name" in str(ei.value)
         assert ctx.merge_reads(b"", 27) == (b"", dict(reads=0, keys=0, chains=0, blocks=0, printed=0, longest_chain=0))
         assert ctx.merge_reads(sel, 27)[0] == golden("merge_readme_k27.txt")     # the context is fine afterwards
+
+
+# ---------------------------------------------------------------- the command line (bin/merge_STR_reads)
+
+CLI = os.path.join(ROOT, "bin", "merge_STR_reads")
+USAGE_MD5 = "05e69bf00e36bbbf150659219c282dad"      # md5 of `merge_STR_reads --help` of the reference (0.3.1), stdout
+
+
+def run_cli(*args):
+    import sys
+    return subprocess.run([sys.executable, CLI] + list(args), capture_output=True)
+
+
+def test_cli_usage_is_the_reference_text():
+    """PrintSimpleUsageString (clparsing.c:268-308) with the options of merge_STR_reads.c:524-531"""
+    import hashlib
+    r = run_cli("--help")
+    assert r.returncode == 0 and hashlib.md5(r.stdout).hexdigest() == USAGE_MD5
+    if os.path.exists(REF_BIN):
+        assert subprocess.run([REF_BIN, "--help"], capture_output=True).stdout == r.stdout
+    r = run_cli()                                   # too few arguments: the usage text and EXIT_FAILURE (:541-544)
+    assert r.returncode == 1 and hashlib.md5(r.stdout).hexdigest() == USAGE_MD5
+    r = run_cli("--bogus", "27", "x.fq")            # clparsing.c:234
+    assert r.returncode == 1 and r.stdout == b"" and b"unknown option bogus" in r.stderr
+    r = run_cli("--min_threshold=abc", "27", "x.fq")
+    assert r.returncode == 1 and b"min_threshold: Expected unsigned int" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_matches_the_reference_binary(tmp_path):
+    for name, src, k, lo, hi, include_all in GOLDENS:
+        path = write(tmp_path, "reads.str.fq", util.gz_read(src))
+        opts = ["--min_threshold=%d" % lo, "--max_threshold=%d" % hi] + (["--all"] if include_all else ["--noall"])
+        r = run_cli(*(opts[:1] + [str(k)] + opts[1:] + [path]))     # options anywhere on the line, as the reference allows
+        assert r.returncode == 0 and r.stdout == golden(name), name
+        nreads = util.gz_read(src).count(b"\n") // 4
+        lines = r.stderr.decode().splitlines()
+        assert lines[0].endswith("]\tProcessing read number 1: " + util.gz_read(src).split(b"\n", 1)[0][1:].decode())
+        assert lines[-1].endswith("]\tProcessed %d reads." % nreads)
+    # gzopen reads gzip and plain alike (fastq_seq.c:9); an even klength is lowered by one with a warning (:557-560)
+    gz = tmp_path / "reads.str.fq.gz"
+    gz.write_bytes(open(os.path.join(ROOT, "tests", "golden", "testdata_readme.out.gz"), "rb").read())
+    r = run_cli("28", str(gz))
+    assert r.returncode == 0 and r.stdout == golden("merge_readme_k27.txt") and b"using 27" in r.stderr
+    r = run_cli("--progress=50", "27", str(gz))
+    assert r.stderr.count(b"Processing read number") == 3 and b"Processing read number 101: " in r.stderr

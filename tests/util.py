@@ -151,3 +151,26 @@ def str_locus_reads(nloci, coverage, L, seed, err=0.01, indel=0.002, ctx=260, sh
             idx += 1
     rng.shuffle(out)
     return "".join(out).encode("latin-1")
+
+
+def genome_reads(nreads, L, genome_len, seed, err=0.01):
+    """reads of both strands from one random genome with substitution errors: real coverage, so
+    most k-mers repeat (what extend_STR_reads is run on), the erroneous ones stay singletons"""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    genome = rng.integers(0, 4, genome_len, dtype=np.uint8)
+    starts = rng.integers(0, genome_len - L, nreads)
+    codes = genome[starts[:, None] + np.arange(L)[None, :]]
+    flip = rng.random(nreads) < 0.5
+    codes[flip] = 3 - codes[flip][:, ::-1]
+    hit = rng.random(codes.shape) < err
+    codes[hit] = (codes[hit] + rng.integers(1, 4, int(hit.sum()), dtype=np.uint8)) & 3
+    bases = np.frombuffer(b"ACGT", np.uint8)[codes]
+    rec = np.empty((nreads, 12 + L + 3 + L + 1), np.uint8)
+    names = np.array([list(b"@g%09d\n" % i) for i in range(nreads)], np.uint8)
+    rec[:, :12] = names
+    rec[:, 12:12 + L] = bases
+    rec[:, 12 + L:12 + L + 3] = np.frombuffer(b"\n+\n", np.uint8)
+    rec[:, 12 + L + 3:12 + 2 * L + 3] = ord("I")
+    rec[:, -1] = 10
+    return rec.tobytes()

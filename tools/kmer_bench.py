@@ -12,7 +12,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from baitstr_b200 import capi                 # noqa: E402
-from tests.test_kmers import genome_reads     # noqa: E402
+from tests.util import genome_reads     # noqa: E402
 
 nreads, L, glen, k = [int(a) for a in sys.argv[1:5]] + [1000000, 150, 3000000, 27][len(sys.argv) - 1:]
 raw = genome_reads(nreads, L, glen, seed=5)
