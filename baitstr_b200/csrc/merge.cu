@@ -28,14 +28,16 @@ constexpr int WARPS = 5;           // chains in flight per CTA: shared memory al
 
 struct WarpShared {
     uint8_t T[T_BYTES];
-    int16_t diag[3][PITCH];
+    int16_t diag[3][MAXF + 1];
     char cons[4][MAXB];
+    char seq[2][MAXF + 1];         // the two flanks being aligned
 };
 static_assert(sizeof(WarpShared) * WARPS <= 227 * 1024, "shared memory of one CTA");
 
 struct WarpExec {
     int lane;
     int16_t *d0, *d1, *d2;
+    char *s1, *s2;
     // Align's matrix (:86-110) along anti-diagonals d = i + j: a cell needs (i, j-1) and (i-1, j) of
     // diagonal d-1 and (i-1, j-1) of d-2, all indexed by their row here
     __device__ __forceinline__ uint64_t dp_fill(const char *t1, int len1, const char *t2, int len2, uint8_t *T)
@@ -43,15 +45,18 @@ struct WarpExec {
         uint64_t best = 0;
         int16_t *p2 = d0, *p1 = d1, *cur = d2;
         if (len1 >= 2 && len2 >= 2) {
+            for (int a = lane; a < len1 - 1; a += 32) s1[a] = t1[a];         // the flanks into shared memory: every cell reads both
+            for (int a = lane; a < len2 - 1; a += 32) s2[a] = t2[a];
+            __syncwarp();
             for (int d = 2; d <= len1 + len2 - 2; d++) {
                 const int ilo = max(1, d - (len2 - 1)), ihi = min(len1 - 1, d - 1);
                 for (int i = ilo + lane; i <= ihi; i += 32) {
                     const int j = d - i;
                     const int left = j >= 2 ? p1[i] : 0, up = i >= 2 ? p1[i - 1] : 0, dg = (i >= 2 && j >= 2) ? p2[i - 1] : 0;
                     unsigned code;
-                    const int a = dp_cell(left, up, dg, t1[i - 1] == t2[j - 1], &code);
+                    const int a = dp_cell(left, up, dg, s1[i - 1] == s2[j - 1], &code);
                     cur[i] = (int16_t)a;
-                    t_put(T, i, j, code);            // cells of one diagonal lie PITCH - 1 apart: never in the same byte
+                    t_put(T, i, j, code);            // cells of one diagonal lie PITCH - 1 apart: never in the same byte, 25 words apart
                     const uint64_t key = best_key(a, i, j);
                     best = key > best ? key : best;
                 }
@@ -78,7 +83,7 @@ k_merge_chains(const Read *reads, const uint32_t *chain_start, const uint32_t *c
 {
     extern __shared__ __align__(16) uint8_t smem[];
     WarpShared *w = reinterpret_cast<WarpShared *>(smem) + (threadIdx.x >> 5);
-    WarpExec x{(int)(threadIdx.x & 31), w->diag[0], w->diag[1], w->diag[2]};
+    WarpExec x{(int)(threadIdx.x & 31), w->diag[0], w->diag[1], w->diag[2], w->seq[0], w->seq[1]};
     const Scratch s{w->T, w->cons[0], w->cons[1], w->cons[2], w->cons[3]};
     for (;;) {
         unsigned t = 0;

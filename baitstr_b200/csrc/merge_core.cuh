@@ -23,10 +23,11 @@ namespace bmerge {
 // Consensus flanks can outgrow the reads (the right flank's overhang is taken from column j of the
 // LONGER sequence, see align_trace), so the bounds leave room beyond a 250-base read's ~215.
 constexpr int MAXF = 383;          // longest flank that can be aligned (DP side = flank + 1 <= 384)
-constexpr int PITCH = 384;         // row pitch of the traceback matrix, in cells
+constexpr int PITCH = 401;         // row pitch of the traceback matrix, in cells: the cells of one anti-diagonal lie PITCH - 1 = 400
+                                   // cells = 25 words apart, an odd number of shared-memory banks, so 32 lanes hit 32 banks
 constexpr int MAXB = 800;          // longest block / consensus sequence held
 constexpr int MAXSUP = 24;         // distinct copy numbers remembered per block
-constexpr int T_BYTES = (MAXF + 1) * PITCH / 4;   // traceback matrix: two bits per cell
+constexpr int T_BYTES = ((MAXF + 1) * PITCH / 4 + 15) / 16 * 16;   // traceback matrix: two bits per cell
 
 enum { ERR_NONE = 0, ERR_FLANK_TOO_LONG = 1, ERR_BLOCK_TOO_LONG = 2, ERR_TOO_MANY_ALLELES = 3 };
 
