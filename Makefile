@@ -5,7 +5,7 @@
 #                   select_STR_reads.so and fastq.so (extension modules under the reference's module
 #                   names), plus libbaitstr_select.so (C ABI + embedded sm_100a code) and the
 #                   Python package with the -c / -d diagnostics; merge_STR_reads (the reference's
-#                   command line over bstr_merge_reads).  extend_STR_reads is not built here.
+#                   command line over bstr_merge_reads) and extend_STR_reads (over bstr_kmers_*).
 PREFIX ?= bin
 PYTHON ?= python3
 
@@ -14,7 +14,7 @@ all:
 
 install: all
 	mkdir -p $(PREFIX)/baitstr_b200
-	[ "$(abspath $(PREFIX))" = "$(abspath bin)" ] || cp bin/select_STR_reads bin/merge_STR_reads bin/VERSION $(PREFIX)/
+	[ "$(abspath $(PREFIX))" = "$(abspath bin)" ] || cp bin/select_STR_reads bin/merge_STR_reads bin/extend_STR_reads bin/VERSION $(PREFIX)/
 	cp baitstr_b200/libbaitstr_select.so $(PREFIX)/
 	cp baitstr_b200/*.py $(PREFIX)/baitstr_b200/
 	$(PYTHON) baitstr_b200/ext/build_ext.py $(PREFIX) $(PREFIX)

@@ -58,7 +58,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
            "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu",
-           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy", "bstr_merge_reads"]
+           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy", "bstr_kmers_extend", "bstr_merge_reads"]
 
 _lib = None
 
@@ -133,6 +133,8 @@ def load_library():
     lib.bstr_kmers_finish.restype = C.c_int
     lib.bstr_kmers_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     lib.bstr_kmers_stats.restype = None
+    lib.bstr_kmers_extend.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_uint64)]
+    lib.bstr_kmers_extend.restype = C.c_int
     lib.bstr_kmers_destroy.argtypes = [C.c_void_p]
     lib.bstr_kmers_destroy.restype = None
     lib.bstr_gunzip_gpu.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
@@ -411,6 +413,33 @@ class Context:
             f.seek(0)
             out = f.read()
         return out, dict(zip(("reads", "keys", "chains", "blocks", "printed", "longest_chain"), [int(x) for x in st]))
+
+    def extend_reads(self, blocks, read_batches, klen, min_threshold=2, max_threshold=255, flanks=1024, expected_kmers=1 << 20):
+        """bstr_kmers_* + bstr_kmers_extend: the extend stage.  blocks = the merge stage's output, read_batches =
+        raw FASTQ batches of the sample's reads (whole records each) -> (the contigs extend_STR_reads would print, stats)."""
+        import tempfile
+        if klen % 2 == 0:
+            klen -= 1                               # extend_STR_reads.c:1072-1075
+        h = self._lib.bstr_kmers_create(self._ctx, int(klen), int(expected_kmers))
+        if not h:
+            self._raise(-3)
+        try:
+            for b in [blocks] + list(read_batches):   # the reference counts its argv[4 ..]: the blocks' file first
+                addr, n, keep = self._addr(b)
+                rc = self._lib.bstr_kmers_add_fastq(h, addr, n)
+                if rc:
+                    self._raise(rc)
+            addr, n, keep = self._addr(blocks)
+            st = (C.c_uint64 * 4)()
+            with tempfile.TemporaryFile() as f:
+                rc = self._lib.bstr_kmers_extend(h, int(min_threshold), int(max_threshold), int(flanks), addr, n, f.fileno(), st)
+                if rc:
+                    self._raise(rc)
+                f.seek(0)
+                out = f.read()
+            return out, dict(zip(("blocks", "contigs", "ends_not_extended", "kmers_kept"), [int(x) for x in st]))
+        finally:
+            self._lib.bstr_kmers_destroy(h)
 
     def count_kmers(self, batches, klen, min_threshold=2, max_threshold=255, expected_kmers=1 << 20):
         """bstr_kmers_*: the k-mer counting pass of extend_STR_reads over raw FASTQ batches (whole

@@ -24,11 +24,12 @@ OPTIONS = [
 ]
 
 
-def usage(version):
+def usage(version, program=None, options=None):
     """PrintSimpleUsageString, clparsing.c:268-308"""
-    out = ["Program : %s (%s)\n" % PROGRAM[:2], "Version : %s\n\n" % version, "usage:\n", "\t%s\n\n" % PROGRAM[2], "options:\n"]
-    width = max(len(o[0]) for o in OPTIONS if o[3])
-    for name, default, valued, documented, text in OPTIONS:
+    program, options = program or PROGRAM, options or OPTIONS
+    out = ["Program : %s (%s)\n" % program[:2], "Version : %s\n\n" % version, "usage:\n", "\t%s\n\n" % program[2], "options:\n"]
+    width = max(len(o[0]) for o in options if o[3])
+    for name, default, valued, documented, text in options:
         if not documented:
             continue
         tail = "[--%s=%s]" % (name, default) if valued else ("[--%s]" % name if default == "TRUE" else "[--no%s]" % name)
@@ -40,9 +41,9 @@ class Die(Exception):
     pass
 
 
-def parse(argv):
+def parse(argv, options=None):
     """ParseOptions, clparsing.c:205-263: --name, --noname, --name=value anywhere; the rest are arguments"""
-    values = dict((o[0], o[1]) for o in OPTIONS)
+    values = dict((o[0], o[1]) for o in (options or OPTIONS))
     rest = []
     for a in argv:
         if a.startswith("--"):

@@ -270,6 +270,22 @@ int bstr_kmers_add_fastq(bstr_kmers *k, const uint8_t *raw, uint64_t nbytes);
 int bstr_kmers_finish(bstr_kmers *k, int min_threshold, int max_threshold, const uint64_t **kmers,
                       const uint8_t **counts, uint64_t *n);
 void bstr_kmers_stats(const bstr_kmers *k, uint64_t out4[4]);
+/* The rest of extend_STR_reads over the same table: the walk through the k-mer graph on both sides of
+ * every merged block and the contigs.  Replaces the block loop of ExtendShortTandemRepeatReads,
+ * /root/reference/src/extend_STR_reads.c:909-998, with ExtendBackward / ExtendForward :471-734,
+ * CheckForSNPBackwards / Forwards :218-438, FindFirstGoodKmer :809-850, PercentIdentity :740-772 and
+ * PrintContig :776-807.  `blocks_fastq` is the merge stage's output; the contigs are written to
+ * out_fd byte for byte as the reference prints them.  A warp walks each block, eight lanes probing
+ * the eight neighbours of a k-mer at once.  As in the reference, the table must have been counted
+ * over the merged blocks' file as well as the read files (it passes argv[4 ..] to the counting pass,
+ * :890-897): call bstr_kmers_add_fastq with the blocks first.
+ *   min_threshold / max_threshold   k-mers outside are not in the table (defaults 2, 255); min >= 2
+ *   flanks                          the --flanks option (default 1024), 2..2048 here
+ *   stats                           NULL or {blocks, contigs printed, ends not extended, k-mers within the thresholds}
+ * A block whose right flank is shorter than klen is skipped (the reference walks on from the bytes
+ * behind the block's text there). */
+int bstr_kmers_extend(bstr_kmers *k, int min_threshold, int max_threshold, int flanks, const uint8_t *blocks_fastq,
+                      uint64_t nbytes, int out_fd, uint64_t stats[4]);
 void bstr_kmers_destroy(bstr_kmers *k);
 
 /* number of CUDA devices visible (0 if none / no driver) */

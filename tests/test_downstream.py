@@ -64,7 +64,7 @@ def test_make_install_layout(tmp_path):
     prefix = str(tmp_path / "bin")
     subprocess.check_call(["make", "-s", "-C", ROOT, "install", "PREFIX=" + prefix], stdout=subprocess.DEVNULL)
     have = set(os.listdir(prefix))
-    assert {"select_STR_reads", "merge_STR_reads", "VERSION", "select_STR_reads.so", "fastq.so", "libbaitstr_select.so", "baitstr_b200"} <= have
+    assert {"select_STR_reads", "merge_STR_reads", "extend_STR_reads", "VERSION", "select_STR_reads.so", "fastq.so", "libbaitstr_select.so", "baitstr_b200"} <= have
     code = ("import sys; sys.path.insert(0, %r)\n"
             "from select_STR_reads import *\n"                      # /root/reference/src/select_STR_reads:61
             "import select_STR_reads as m, fastq\n"
@@ -141,3 +141,23 @@ def test_gpu_select_and_merge_feed_reference_extend(tmp_path):
     contigs = subprocess.run([extend, "4000", "20", "27", str(tmp_path / "merged.reads.str.fq")] + reads, capture_output=True,
                              check=True).stdout
     _check(merged.decode().splitlines(), contigs.decode().splitlines())
+
+
+@pytest.mark.gpu
+def test_gpu_whole_pipeline_from_this_repository(tmp_path):
+    """README.md:265-287 with all three stages from this repository (test_data/Makefile:5-12):
+    bin/select_STR_reads -i -n 3 -f 29 | bin/merge_STR_reads 27 | bin/extend_STR_reads 4000 20 27 --
+    the block and the contig of the reference's walk-through, byte for byte its goldens."""
+    reads = []
+    for i in (1, 2):
+        p = tmp_path / ("Illumina_100_500_%d.fq" % i)
+        p.write_bytes(util.gz_read("testdata_%d.fq.gz" % i))
+        reads.append(str(p))
+    run = lambda exe, *args: subprocess.run([sys.executable, os.path.join(ROOT, "bin", exe)] + list(args), capture_output=True, check=True).stdout
+    (tmp_path / "reads.str.fq").write_bytes(run("select_STR_reads", "-i", "-n", "3", "-f", "29", *reads))
+    merged = run("merge_STR_reads", "27", str(tmp_path / "reads.str.fq"))
+    (tmp_path / "merged.reads.str.fq").write_bytes(merged)
+    contigs = run("extend_STR_reads", "4000", "20", "27", str(tmp_path / "merged.reads.str.fq"), *reads)
+    _check(merged.decode().splitlines(), contigs.decode().splitlines())
+    golden = lambda n: open(os.path.join(ROOT, "tests", "golden", n), "rb").read()
+    assert merged == golden("merge_readme_k27.txt") and contigs == golden("extend_readme.txt")

@@ -170,3 +170,164 @@ def test_gpu_errors_are_loud(capi):
             ctx.count_kmers([raw[:-1]], 21)
         assert ctx.count_kmers([], 21)[0].size == 0
         assert ctx.count_kmers([raw], 21)[2]["records"] == 4000   # the context is fine afterwards
+
+
+# ---------------------------------------------------------------- the extension walk (bstr_kmers_extend)
+#
+# The rest of extend_STR_reads over the counted table: extend_STR_reads.c:195-998.  Checkers: the
+# reference's own binary (oracle/_ref/downstream/extend_STR_reads, compiled in place) and the golden it
+# wrote for the README's walk-through (tests/golden/extend_readme.txt, make_extend_golden.sh).
+# not gpu: the product's walk (csrc/extend_core.cuh, extend_plan.h) built for the host with a sequential
+#          executor (tests/emul/emul_extend.cpp) over the table the reference's counting function dumps
+# gpu:     counting + walks on the device through the C ABI, and through bin/extend_STR_reads
+
+EXTEND_BIN = os.path.join(ROOT, "oracle", "_ref", "downstream", "extend_STR_reads")
+MERGE_BIN = os.path.join(ROOT, "oracle", "_ref", "downstream", "merge_STR_reads")
+EMUL_SRC = os.path.join(ROOT, "tests", "emul", "emul_extend.cpp")
+EMUL_BIN = os.path.join(ROOT, "tests", "emul", "_build", "emul_extend")
+EXTEND_USAGE_MD5 = "6d81c3d9b46af6dc328c63bd14a88b84"     # md5 of `extend_STR_reads --help` of the reference (0.3.1), stdout
+needs_bins = pytest.mark.skipif(not (os.path.exists(EXTEND_BIN) and os.path.exists(MERGE_BIN) and os.path.exists(REF_BIN)),
+                                reason="oracle/_ref/downstream not built (oracle/build_downstream.sh)")
+
+DIPLOID = [
+    # name, (genome_len, nloci, coverage, read length, seed, repeat_len), [(klen, flanks, min, max)]
+    ("150bp", (40000, 30, 40, 150, 1, 0), [(27, 1024, 2, 255), (27, 100, 2, 255), (21, 1024, 4, 60)]),
+    ("100bp_with_repeats", (50000, 40, 30, 100, 2, 400), [(27, 1024, 2, 255), (31, 1024, 2, 255), (27, 1024, 10, 255)]),
+    ("250bp", (30000, 12, 50, 250, 3, 0), [(27, 1024, 2, 255), (25, 300, 3, 255)]),
+]
+
+
+def emul_extend_bin():
+    csrc = os.path.join(ROOT, "baitstr_b200", "csrc")
+    deps = [EMUL_SRC, os.path.join(csrc, "extend_core.cuh"), os.path.join(csrc, "extend_plan.h")]
+    if not os.path.exists(EMUL_BIN) or os.path.getmtime(EMUL_BIN) < max(os.path.getmtime(d) for d in deps):
+        os.makedirs(os.path.dirname(EMUL_BIN), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-o", EMUL_BIN, EMUL_SRC])
+    return EMUL_BIN
+
+
+_diploid = {}
+
+
+def diploid_case(name, tmp_path):
+    """reads -> select (oracle) -> merge (the reference's binary): paths of blocks and the two read files"""
+    if name not in _diploid:
+        from oracle import oracle
+        args = dict((n, a) for n, a, _ in DIPLOID)[name]
+        raw = util.diploid_str_reads(args[0], args[1], args[2], args[3], args[4], repeat_len=args[5])
+        recs = raw.split(b"\n@")
+        half = len(recs) // 2
+        r1, r2 = b"\n@".join(recs[:half]) + b"\n", b"@" + b"\n@".join(recs[half:])
+        sel = oracle.select_buffer(raw, n=3)
+        p = tmp_path / "sel.fq"
+        p.write_bytes(sel)
+        merged = subprocess.run([MERGE_BIN, "--all", "--min_threshold=3", "27", str(p)], check=True, capture_output=True).stdout
+        _diploid[name] = (merged, r1, r2)
+    merged, r1, r2 = _diploid[name]
+    paths = []
+    for fn, data in (("merged.fq", merged), ("r1.fq", r1), ("r2.fq", r2)):
+        q = tmp_path / fn
+        q.write_bytes(data)
+        paths.append(str(q))
+    return paths, (merged, r1, r2)
+
+
+def reference_extend(paths, klen, flanks, lo, hi):
+    return subprocess.run([EXTEND_BIN, "--min_threshold=%d" % lo, "--max_threshold=%d" % hi, "--flanks=%d" % flanks, "4000000", "20", str(klen)] + paths,
+                          check=True, capture_output=True).stdout
+
+
+def test_extend_golden_is_the_readme_known_answer():
+    """README.md:265-287: one contig for the shipped test_data"""
+    with open(os.path.join(ROOT, "tests", "golden", "extend_readme.txt"), "rb") as f:
+        assert f.read().split(b"\n")[0] == b">Block1\tTC:7,5:191:205"
+
+
+@needs_bins
+@pytest.mark.parametrize("case", DIPLOID, ids=[d[0] for d in DIPLOID])
+def test_host_build_of_the_walk_matches_the_reference_binary(case, tmp_path):
+    name, _, runs = case
+    paths, _ = diploid_case(name, tmp_path)
+    contigs = 0
+    for klen, flanks, lo, hi in runs:
+        want = reference_extend(paths, klen, flanks, lo, hi)
+        dump = tmp_path / "kmers.txt"
+        dump.write_bytes(subprocess.run([REF_BIN, str(klen), str(lo), str(hi), "4000000"] + paths, check=True, capture_output=True).stdout)
+        got = subprocess.run([emul_extend_bin(), str(klen), str(flanks), str(dump), paths[0]], check=True, capture_output=True).stdout
+        assert got == want, (klen, flanks, lo, hi)
+        contigs += want.count(b">")
+        if flanks >= 1024:
+            assert max(len(ln) for ln in want.split(b"\n")) > 800     # the walks go far beyond the blocks
+    assert contigs > 100
+
+
+def test_extend_cli_usage_is_the_reference_text():
+    import hashlib
+    import sys
+    cli = os.path.join(ROOT, "bin", "extend_STR_reads")
+    r = subprocess.run([sys.executable, cli, "--help"], capture_output=True)
+    assert r.returncode == 0 and hashlib.md5(r.stdout).hexdigest() == EXTEND_USAGE_MD5
+    if os.path.exists(EXTEND_BIN):
+        assert subprocess.run([EXTEND_BIN, "--help"], capture_output=True).stdout == r.stdout
+    r = subprocess.run([sys.executable, cli, "4000", "20", "27", "blocks.fq", "reads1.fq"], capture_output=True)   # argc < 7 (:1046-1049)
+    assert r.returncode == 1 and hashlib.md5(r.stdout).hexdigest() == EXTEND_USAGE_MD5
+    r = subprocess.run([sys.executable, cli, "--flank=3", "4000", "20", "27", "a", "b", "c"], capture_output=True)
+    assert r.returncode == 1 and b"unknown option flank" in r.stderr
+
+
+@pytest.mark.gpu
+def test_gpu_extend_test_data_matches_the_reference_golden(capi):
+    blocks = open(os.path.join(ROOT, "tests", "golden", "merge_readme_k27.txt"), "rb").read()
+    reads = [util.gz_read("testdata_%d.fq.gz" % i) for i in (1, 2)]
+    with capi.Context() as ctx:
+        out, st = ctx.extend_reads(blocks, reads, 27, expected_kmers=200000)
+    assert out == open(os.path.join(ROOT, "tests", "golden", "extend_readme.txt"), "rb").read()
+    assert st["blocks"] == 1 and st["contigs"] == 1 and st["ends_not_extended"] == 0 and st["kmers_kept"] >= 2013
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", DIPLOID, ids=[d[0] for d in DIPLOID])
+def test_gpu_extend_matches_the_reference_binary(capi, case, tmp_path):
+    if not (os.path.exists(EXTEND_BIN) and os.path.exists(MERGE_BIN)):
+        pytest.skip("oracle/_ref/downstream not built")
+    name, _, runs = case
+    paths, (merged, r1, r2) = diploid_case(name, tmp_path)
+    with capi.Context() as ctx:
+        for klen, flanks, lo, hi in runs:
+            out, st = ctx.extend_reads(merged, [r1, r2], klen, lo, hi, flanks, expected_kmers=1 << 22)
+            assert out == reference_extend(paths, klen, flanks, lo, hi), (klen, flanks, lo, hi)
+            assert st["blocks"] == merged.count(b"\n") // 4 and st["contigs"] == out.count(b">")
+
+
+@pytest.mark.gpu
+def test_gpu_extend_cli_and_errors(capi, tmp_path):
+    import sys
+    cli = os.path.join(ROOT, "bin", "extend_STR_reads")
+    paths = []
+    for fn, data in (("merged.reads.str.fq", open(os.path.join(ROOT, "tests", "golden", "merge_readme_k27.txt"), "rb").read()),
+                     ("reads_1.fq", util.gz_read("testdata_1.fq.gz")), ("reads_2.fq.gz", gzip.compress(util.gz_read("testdata_2.fq.gz")))):
+        p = tmp_path / fn
+        p.write_bytes(data)
+        paths.append(str(p))
+    r = subprocess.run([sys.executable, cli, "4000", "20", "27"] + paths, capture_output=True)       # test_data/Makefile:10-12
+    assert r.returncode == 0 and r.stdout == open(os.path.join(ROOT, "tests", "golden", "extend_readme.txt"), "rb").read(), r.stderr[-2000:]
+    assert b"Expecting 23633 kmers in this dataset with haploid genome size 4000 bps." in r.stderr
+    r = subprocess.run([sys.executable, cli, "--flanks=60", "4000", "20", "28"] + paths, capture_output=True)
+    assert r.returncode == 0 and b"using 27" in r.stderr
+    if os.path.exists(EXTEND_BIN):
+        plain = tmp_path / "reads_2.fq"
+        plain.write_bytes(util.gz_read("testdata_2.fq.gz"))
+        assert r.stdout == reference_extend(paths[:2] + [str(plain)], 27, 60, 2, 255)
+    blocks = open(paths[0], "rb").read()
+    with capi.Context() as ctx:
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.extend_reads(blocks, [util.gz_read("testdata_1.fq.gz")], 27, min_threshold=1)
+        assert "min_threshold" in str(ei.value)
+        with pytest.raises(capi.BstrError) as ei:
+            ctx.extend_reads(blocks, [util.gz_read("testdata_1.fq.gz")], 27, flanks=5000)
+        assert "flanks" in str(ei.value)
+        with pytest.raises(capi.BstrError) as ei:            # not the merge stage's output
+            ctx.extend_reads(util.gz_read("testdata_1.fq.gz")[:2000].rsplit(b"\n@", 1)[0] + b"\n", [], 27)
+        assert "parsing the name" in str(ei.value)
+        out, st = ctx.extend_reads(blocks, [util.gz_read("testdata_1.fq.gz")], 31)      # klen > the block's left flank? no: 60 >= 31; still one contig or none, and no crash
+        assert st["blocks"] == 1

@@ -174,3 +174,50 @@ def genome_reads(nreads, L, genome_len, seed, err=0.01):
     rec[:, 12 + L + 3:12 + 2 * L + 3] = ord("I")
     rec[:, -1] = 10
     return rec.tobytes()
+
+
+def diploid_str_reads(genome_len, nloci, coverage, L, seed, snp_every=250, err=0.004, repeat_len=0):
+    """Reads of both strands from a diploid genome with `nloci` STR loci (different copy numbers on the
+    two haplotypes) and a SNP about every `snp_every` bases: what the extend stage walks through --
+    long unique stretches, heterozygous forks that close again (bubbles), forks that do not (indels of
+    the STR alleles), and with repeat_len > 0 a repeated segment (walks that meet themselves)."""
+    rng = random.Random(seed)
+    step = genome_len // (nloci + 1)
+    hap_a, hap_b = [], []
+    repeat = "".join(rng.choice("ACGT") for _ in range(repeat_len))
+    for locus in range(nloci + 1):
+        unique = "".join(rng.choice("ACGT") for _ in range(step))
+        if repeat_len and locus % 3 == 1:
+            unique = unique[:step // 2] + repeat + unique[step // 2:]
+        other = list(unique)
+        for i in range(len(other)):
+            if rng.random() < 1.0 / snp_every:
+                other[i] = rng.choice([b for b in "ACGT" if b != other[i]])
+        hap_a.append(unique)
+        hap_b.append("".join(other))
+        if locus < nloci:
+            k = rng.randint(2, 6)
+            while True:
+                motif = "".join(rng.choice("ACGT") for _ in range(k))
+                if len(set(motif)) > 1:
+                    break
+            c = rng.randint(5, 12)
+            hap_a.append(motif * c)
+            hap_b.append(motif * (c if rng.random() < 0.3 else max(3, c + rng.choice([-2, -1, 1, 2, 3]))))
+    haps = ["".join(hap_a), "".join(hap_b)]
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A"}
+    nreads = coverage * len(haps[0]) // L
+    out = []
+    for idx in range(nreads):
+        hap = haps[idx & 1]
+        start = rng.randint(0, len(hap) - L)
+        s = list(hap[start:start + L])
+        for i in range(L):
+            if rng.random() < err:
+                s[i] = rng.choice([b for b in "ACGT" if b != s[i]])
+        s = "".join(s)
+        if rng.random() < 0.5:
+            s = "".join(comp[b] for b in reversed(s))
+        q = "".join(chr(rng.choice([40, 50, 53, 54, 60, 70, 73])) if rng.random() < 0.1 else "I" for _ in range(L))
+        out.append("@d.%08d/1\n%s\n+\n%s\n" % (idx, s, q))
+    return "".join(out).encode("latin-1")
