@@ -597,6 +597,35 @@ def next_stages(device):
                 want = [tuple(int(x) for x in ln.split()) for ln in ref.decode().splitlines()]
                 k["identical_to_reference"] = want == list(zip(kmers.tolist(), counts.tolist()))
             out["extend_STR_reads_kmer_count"] = k
+            # the whole extend stage: 50 k reads of a 0.25 Mb diploid genome -> select, merge (GPU) -> k-mer counting + walks
+            raw = util.diploid_str_reads(250000, 250, 30, 150, seed=31)
+            nreads = raw.count(b"\n") // 4
+            recs = raw.split(b"\n@")
+            r1, r2 = b"\n@".join(recs[:len(recs) // 2]) + b"\n", b"@" + b"\n@".join(recs[len(recs) // 2:])
+            with capi.Context(devices=[device], n=3) as c3:
+                sel = c3.scan_batch(raw)[0]
+            merged, _ = ctx.merge_reads(sel, 27, 3, 10000, True)
+            expected = nreads * 124 // 2 + 500000
+            ctx.extend_reads(merged, [r1[: r1.index(b"\n@", len(r1) // 20) + 1]], 27, expected_kmers=expected // 10)
+            best = 1e9
+            for _ in range(3):
+                t0 = time.perf_counter()
+                got, st = ctx.extend_reads(merged, [r1, r2], 27, expected_kmers=expected)
+                best = min(best, time.perf_counter() - t0)
+            e = {"reads": nreads, "k": 27, "blocks": st["blocks"], "contigs": st["contigs"], "reads_per_s": round(nreads / best, 1),
+                 "ms": round(best * 1e3, 2), "reference_reads_per_s": None, "identical_to_reference": None}
+            exe = os.path.join(down, "extend_STR_reads")
+            if os.path.exists(exe):
+                paths = []
+                for fn, data in (("merged.fq", merged), ("r1.fq", r1), ("r2.fq", r2)):
+                    with open(os.path.join(tmp, fn), "wb") as f:
+                        f.write(data)
+                    paths.append(os.path.join(tmp, fn))
+                t0 = time.perf_counter()
+                want = subprocess.run([exe, "250000", "30", "27"] + paths, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout
+                e["reference_reads_per_s"] = round(nreads / (time.perf_counter() - t0), 1)
+                e["identical_to_reference"] = want == got
+            out["extend_STR_reads"] = e
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
     for name, v in out.items():
