@@ -58,7 +58,7 @@ EXPORTS = ["bstr_create", "bstr_destroy", "bstr_last_error", "bstr_run_files", "
            "bstr_get_stats", "bstr_reset_stats", "bstr_device_count", "bstr_lanes",
            "bstr_submit_batch", "bstr_collect_batch", "bstr_gunzip", "bstr_debug_reads",
            "bstr_debug_codes_cap", "bstr_geometry_probe", "bstr_pcie_probe", "bstr_scan_batch_noalloc", "bstr_gunzip_gpu",
-           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy", "bstr_kmers_extend", "bstr_merge_reads"]
+           "bstr_kmers_create", "bstr_kmers_add_fastq", "bstr_kmers_add_resident", "bstr_kmers_finish", "bstr_kmers_stats", "bstr_kmers_destroy", "bstr_kmers_extend", "bstr_merge_reads"]
 
 _lib = None
 
@@ -129,6 +129,8 @@ def load_library():
     lib.bstr_kmers_create.restype = C.c_void_p
     lib.bstr_kmers_add_fastq.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.bstr_kmers_add_fastq.restype = C.c_int
+    lib.bstr_kmers_add_resident.argtypes = [C.c_void_p, C.c_uint64]
+    lib.bstr_kmers_add_resident.restype = C.c_int
     lib.bstr_kmers_finish.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.bstr_kmers_finish.restype = C.c_int
     lib.bstr_kmers_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
@@ -201,6 +203,62 @@ class PinnedBuffer:
             self.close()
         except Exception:
             pass
+
+
+class KmerCounter:
+    """bstr_kmers_*: the k-mer table of extend_STR_reads on the GPU (include/baitstr_select.h)."""
+
+    def __init__(self, ctx, klen, expected_kmers=1 << 20):
+        self._ctx, self._lib = ctx, ctx._lib
+        self._h = self._lib.bstr_kmers_create(ctx._ctx, int(klen), int(expected_kmers))
+        if not self._h:
+            ctx._raise(-3)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def close(self):
+        if self._h:
+            self._lib.bstr_kmers_destroy(self._h)
+            self._h = None
+
+    def _check(self, rc):
+        if rc:
+            self._ctx._raise(rc)
+
+    def add_fastq(self, raw):
+        addr, n, keep = Context._addr(raw)
+        self._check(self._lib.bstr_kmers_add_fastq(self._h, addr, n))
+
+    def add_resident(self, nbytes):
+        """count the batch bstr_scan_batch has just scanned on this context, where it lies in device memory"""
+        self._check(self._lib.bstr_kmers_add_resident(self._h, int(nbytes)))
+
+    def finish(self, min_threshold=2, max_threshold=255):
+        kp, cp, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        self._check(self._lib.bstr_kmers_finish(self._h, int(min_threshold), int(max_threshold), C.byref(kp), C.byref(cp), C.byref(n)))
+        if not n.value:
+            return np.zeros(0, np.uint64), np.zeros(0, np.uint8)
+        return (np.ctypeslib.as_array((C.c_uint64 * n.value).from_address(kp.value)).copy(),
+                np.ctypeslib.as_array((C.c_uint8 * n.value).from_address(cp.value)).copy())
+
+    def extend(self, blocks, min_threshold=2, max_threshold=255, flanks=1024):
+        import tempfile
+        addr, n, keep = Context._addr(blocks)
+        st = (C.c_uint64 * 4)()
+        with tempfile.TemporaryFile() as f:
+            self._check(self._lib.bstr_kmers_extend(self._h, int(min_threshold), int(max_threshold), int(flanks), addr, n, f.fileno(), st))
+            f.seek(0)
+            out = f.read()
+        return out, dict(zip(("blocks", "contigs", "ends_not_extended", "kmers_kept"), [int(x) for x in st]))
+
+    def stats(self):
+        st = (C.c_uint64 * 4)()
+        self._lib.bstr_kmers_stats(self._h, st)
+        return dict(zip(("records", "kmers", "distinct", "slots"), [int(x) for x in st]))
 
 
 class Context:
@@ -414,59 +472,28 @@ class Context:
             out = f.read()
         return out, dict(zip(("reads", "keys", "chains", "blocks", "printed", "longest_chain"), [int(x) for x in st]))
 
+    def kmer_counter(self, klen, expected_kmers=1 << 20):
+        """a bstr_kmers handle on this context (use as a context manager)"""
+        return KmerCounter(self, klen, expected_kmers)
+
     def extend_reads(self, blocks, read_batches, klen, min_threshold=2, max_threshold=255, flanks=1024, expected_kmers=1 << 20):
         """bstr_kmers_* + bstr_kmers_extend: the extend stage.  blocks = the merge stage's output, read_batches =
         raw FASTQ batches of the sample's reads (whole records each) -> (the contigs extend_STR_reads would print, stats)."""
-        import tempfile
         if klen % 2 == 0:
             klen -= 1                               # extend_STR_reads.c:1072-1075
-        h = self._lib.bstr_kmers_create(self._ctx, int(klen), int(expected_kmers))
-        if not h:
-            self._raise(-3)
-        try:
+        with self.kmer_counter(klen, expected_kmers) as kc:
             for b in [blocks] + list(read_batches):   # the reference counts its argv[4 ..]: the blocks' file first
-                addr, n, keep = self._addr(b)
-                rc = self._lib.bstr_kmers_add_fastq(h, addr, n)
-                if rc:
-                    self._raise(rc)
-            addr, n, keep = self._addr(blocks)
-            st = (C.c_uint64 * 4)()
-            with tempfile.TemporaryFile() as f:
-                rc = self._lib.bstr_kmers_extend(h, int(min_threshold), int(max_threshold), int(flanks), addr, n, f.fileno(), st)
-                if rc:
-                    self._raise(rc)
-                f.seek(0)
-                out = f.read()
-            return out, dict(zip(("blocks", "contigs", "ends_not_extended", "kmers_kept"), [int(x) for x in st]))
-        finally:
-            self._lib.bstr_kmers_destroy(h)
+                kc.add_fastq(b)
+            return kc.extend(blocks, min_threshold, max_threshold, flanks)
 
     def count_kmers(self, batches, klen, min_threshold=2, max_threshold=255, expected_kmers=1 << 20):
         """bstr_kmers_*: the k-mer counting pass of extend_STR_reads over raw FASTQ batches (whole
         records each).  Returns (uint64 k-mers sorted, uint8 counts, stats dict)."""
-        h = self._lib.bstr_kmers_create(self._ctx, int(klen), int(expected_kmers))
-        if not h:
-            self._raise(-3)
-        try:
+        with self.kmer_counter(klen, expected_kmers) as kc:
             for b in batches:
-                addr, n, keep = self._addr(b)
-                rc = self._lib.bstr_kmers_add_fastq(h, addr, n)
-                if rc:
-                    self._raise(rc)
-            kp, cp, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
-            rc = self._lib.bstr_kmers_finish(h, int(min_threshold), int(max_threshold), C.byref(kp), C.byref(cp), C.byref(n))
-            if rc:
-                self._raise(rc)
-            if n.value:
-                kmers = np.ctypeslib.as_array((C.c_uint64 * n.value).from_address(kp.value)).copy()
-                counts = np.ctypeslib.as_array((C.c_uint8 * n.value).from_address(cp.value)).copy()
-            else:
-                kmers, counts = np.zeros(0, np.uint64), np.zeros(0, np.uint8)
-            st = (C.c_uint64 * 4)()
-            self._lib.bstr_kmers_stats(h, st)
-            return kmers, counts, dict(zip(("records", "kmers", "distinct", "slots"), [int(x) for x in st]))
-        finally:
-            self._lib.bstr_kmers_destroy(h)
+                kc.add_fastq(b)
+            kmers, counts = kc.finish(min_threshold, max_threshold)
+            return kmers, counts, kc.stats()
 
     def stats(self):
         st = Stats()

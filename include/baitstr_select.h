@@ -262,11 +262,17 @@ int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nbytes, int k
  * its Bloom filter's false positives (seeded from time()).
  *   create     expected_kmers = distinct k-mers the table must hold, singletons included
  *   add_fastq  raw FASTQ in host memory: whole 4-line records, newline-terminated; any number of calls
+ *   add_resident  see below
  *   finish     the arrays belong to the handle and stay valid until it is destroyed
  *   stats      out4 = {records, k-mers counted, distinct k-mers, table slots} */
 typedef struct bstr_kmers bstr_kmers;
 bstr_kmers *bstr_kmers_create(bstr_ctx *ctx, int klen, uint64_t expected_kmers);
 int bstr_kmers_add_fastq(bstr_kmers *k, const uint8_t *raw, uint64_t nbytes);
+/* The same for the batch the select stage has just scanned: bstr_scan_batch leaves its input in device
+ * memory, and the first nbytes of it (<= the `consumed` it reported: whole records) are counted where
+ * they lie -- the reads cross PCIe once for both stages.  The handle must belong to the context that
+ * ran bstr_scan_batch; no other batch call in between. */
+int bstr_kmers_add_resident(bstr_kmers *k, uint64_t nbytes);
 int bstr_kmers_finish(bstr_kmers *k, int min_threshold, int max_threshold, const uint64_t **kmers,
                       const uint8_t **counts, uint64_t *n);
 void bstr_kmers_stats(const bstr_kmers *k, uint64_t out4[4]);

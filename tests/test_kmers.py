@@ -151,6 +151,32 @@ def test_gpu_larger_input_against_the_reference_binary(capi, tmp_path):
 
 
 @pytest.mark.gpu
+def test_gpu_counts_the_batch_the_select_stage_left_resident(capi):
+    """bstr_kmers_add_resident: the reads cross PCIe once for the select stage and the counting pass"""
+    raws = [genome_reads(30000, 150, 200000, seed=5), genome_reads(20000, 100, 200000, seed=6)]
+    with capi.Context() as ctx:
+        want = gpu_pairs(ctx, raws, 27)[0]
+        with ctx.kmer_counter(27, 1 << 22) as kc:
+            with pytest.raises(capi.BstrError) as ei:          # nothing scanned yet on this context
+                kc.add_resident(1000)
+            assert "resident" in str(ei.value)
+            selected = b""
+            for raw in raws:
+                cut = raw + raw[:200]                          # a batch that ends inside a record: only whole records count
+                out, info = ctx.scan_batch(cut, final=False)
+                assert info["consumed"] == len(raw)
+                kc.add_resident(info["consumed"])
+                selected += out
+            with pytest.raises(capi.BstrError):                # more than the batch holds
+                kc.add_resident(len(cut) + 1)
+            kmers, counts = kc.finish()
+            assert [(int(k), int(c)) for k, c in zip(kmers, counts)] == want
+            assert kc.stats()["records"] == 50000
+        from oracle import oracle
+        assert selected == b"".join(oracle.select_buffer(r) for r in raws)     # and the select output is what it always is
+
+
+@pytest.mark.gpu
 def test_gpu_errors_are_loud(capi):
     raw = util.synth_fastq(4000, 100, seed=11)
     with capi.Context() as ctx:
