@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <memory>
 #include <numeric>
 
 #include "host_common.h"
@@ -108,13 +109,51 @@ __global__ void k_merge_init(BlockHead *heads, uint32_t nkeys)
     if (k < nkeys) { BlockHead h; memset(&h, 0, sizeof h); h.created_by = -1; heads[k] = h; }
 }
 
-// the sequences of the blocks that will be printed, side by side
-__global__ void k_merge_gather(const uint32_t *which, uint32_t n, const char *bseqs, const char *bquals, char *oseq, char *oqual)
+// the reverse strand of every read (ReverseComplementSequence, fastq_seq.c:153-176): a warp per read
+__global__ void k_merge_strands(const Read *reads, uint32_t nreads, const char *fwd, const char *qfwd, char *rev, char *qrev)
+{
+    const uint32_t r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= nreads) return;
+    const uint32_t off = reads[r].off, L = reads[r].slen;
+    for (uint32_t i = threadIdx.x & 31; i < L; i += 32) {
+        const unsigned char c = (unsigned char)fwd[off + L - 1 - i], u = c & 0xDF, low = c & 0x20;
+        // the IUPAC complement in either case, a blank for everything else (the table of fastq_seq.c:146-150)
+        unsigned char o = ' ';
+        if (c >= 64 && c < 128) {
+            switch (u) {
+            case 'A': o = 'T'; break; case 'T': o = 'A'; break; case 'C': o = 'G'; break; case 'G': o = 'C'; break;
+            case 'B': o = 'V'; break; case 'V': o = 'B'; break; case 'D': o = 'H'; break; case 'H': o = 'D'; break;
+            case 'K': o = 'M'; break; case 'M': o = 'K'; break; case 'R': o = 'Y'; break; case 'Y': o = 'R'; break;
+            case 'N': o = 'N'; break; case 'S': o = 'S'; break; case 'W': o = 'W'; break; case 'X': o = 'X'; break;
+            default: break;
+            }
+            if (o != ' ') o |= low;
+        }
+        rev[off + i] = (char)o;
+        qrev[off + i] = qfwd[off + L - 1 - i];
+    }
+    if ((threadIdx.x & 31) == 0) { rev[off + L] = 0; qrev[off + L] = 0; }
+}
+
+// what the host needs of EVERY key: who created its block (the order of the reference's map) and whether it is printed
+__global__ void k_merge_verdicts(const BlockHead *heads, uint32_t nkeys, uint32_t lo, uint32_t hi, int include_all, int32_t *created_by, uint8_t *print)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nkeys) return;
+    const BlockHead h = heads[k];
+    created_by[k] = h.created_by;
+    print[k] = h.created_by >= 0 && block_verdict(h, lo, hi, include_all != 0).print;
+}
+
+// the blocks that will be printed, side by side
+__global__ void k_merge_gather(const uint32_t *which, uint32_t n, const BlockHead *heads, const char *bseqs, const char *bquals, BlockHead *ohead,
+                               char *oseq, char *oqual)
 {
     const uint32_t b = blockIdx.x;
     if (b >= n) return;
     const size_t from = (size_t)which[b] * MAXB, to = (size_t)b * MAXB;
     for (int a = threadIdx.x; a < MAXB; a += blockDim.x) { oseq[to + a] = bseqs[from + a]; oqual[to + a] = bquals[from + a]; }
+    if (threadIdx.x == 0) ohead[b] = heads[which[b]];
 }
 
 static const char *err_text(int e)
@@ -153,7 +192,7 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
     }
     const auto t0 = std::chrono::steady_clock::now();
     Plan P;
-    if (!make_plan(fastq, nbytes, klength, P)) { set_error(ctx, "bstr_merge_reads: %s", P.error.c_str()); return BSTR_ERR_PARAM; }
+    if (!make_plan(fastq, nbytes, klength, P, 0, false)) { set_error(ctx, "bstr_merge_reads: %s", P.error.c_str()); return BSTR_ERR_PARAM; }
     const uint32_t nreads = (uint32_t)P.reads.size(), nkeys = (uint32_t)P.keys.size(), nchains = (uint32_t)P.chain_start.size() - 1;
     std::string out;
     uint64_t st_blocks = 0, st_printed = 0, st_longest = 0;
@@ -169,7 +208,7 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
         const auto t1 = std::chrono::steady_clock::now();
         CUDA_TRY(cudaSetDevice(ctx->dev));
         cudaStream_t st = ctx->stream;
-        DevBuf d_reads, d_cs, d_cr, d_co, d_heads, d_bseq, d_bqual, d_fwd, d_qfwd, d_rev, d_qrev, d_misc, d_which, d_oseq, d_oqual;
+        DevBuf d_reads, d_cs, d_cr, d_co, d_heads, d_bseq, d_bqual, d_fwd, d_qfwd, d_rev, d_qrev, d_misc, d_which, d_oseq, d_oqual, d_made, d_print, d_ohead;
         const size_t blob = P.fwd.size();
 #define BM_UP(buf, src, bytes)                                                                                     \
         do {                                                                                                           \
@@ -182,14 +221,17 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
         BM_UP(d_co, order.data(), (size_t)nchains * 4);
         BM_UP(d_fwd, P.fwd.data(), blob);
         BM_UP(d_qfwd, P.qfwd.data(), blob);
-        BM_UP(d_rev, P.rev.data(), blob);
-        BM_UP(d_qrev, P.qrev.data(), blob);
+        BM_UP(d_rev, (const void *)nullptr, blob);
+        BM_UP(d_qrev, (const void *)nullptr, blob);
+        BM_UP(d_made, (const void *)nullptr, (size_t)nkeys * 4);
+        BM_UP(d_print, (const void *)nullptr, (size_t)nkeys);
         BM_UP(d_heads, (const void *)nullptr, (size_t)nkeys * sizeof(BlockHead));
         BM_UP(d_bseq, (const void *)nullptr, (size_t)nkeys * MAXB);
         BM_UP(d_bqual, (const void *)nullptr, (size_t)nkeys * MAXB);
         BM_UP(d_misc, (const void *)nullptr, 16);
         CUDA_TRY(cudaMemsetAsync(d_misc.p, 0, 16, st));
         k_merge_init<<<(nkeys + 255) / 256, 256, 0, st>>>(d_heads.as<BlockHead>(), nkeys);
+        k_merge_strands<<<(nreads + 7) / 8, 256, 0, st>>>(d_reads.as<Read>(), nreads, d_fwd.as<char>(), d_qfwd.as<char>(), d_rev.as<char>(), d_qrev.as<char>());
         const size_t smem = sizeof(WarpShared) * WARPS;
         CUDA_TRY(cudaFuncSetAttribute(k_merge_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaEvent_t e0, e1;
@@ -203,9 +245,13 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
         cudaEventRecord(e1, st);
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return cuda_fail(ctx, le, "k_merge_chains", __LINE__); }
-        std::vector<BlockHead> heads(nkeys);
+        k_merge_verdicts<<<(nkeys + 255) / 256, 256, 0, st>>>(d_heads.as<BlockHead>(), nkeys, (uint32_t)min_threshold, (uint32_t)max_threshold, include_all,
+                                                              d_made.as<int32_t>(), d_print.as<uint8_t>());
+        std::unique_ptr<int32_t[]> made(new int32_t[nkeys]);
+        std::unique_ptr<uint8_t[]> printed(new uint8_t[nkeys]);
         int misc[4] = {0, 0, 0, 0};
-        cudaError_t ce = cudaMemcpyAsync(heads.data(), d_heads.p, (size_t)nkeys * sizeof(BlockHead), cudaMemcpyDeviceToHost, st);
+        cudaError_t ce = cudaMemcpyAsync(made.get(), d_made.p, (size_t)nkeys * 4, cudaMemcpyDeviceToHost, st);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(printed.get(), d_print.p, (size_t)nkeys, cudaMemcpyDeviceToHost, st);
         if (ce == cudaSuccess) ce = cudaMemcpyAsync(misc, d_misc.p, 16, cudaMemcpyDeviceToHost, st);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
         float kms = 0;
@@ -218,33 +264,36 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
             return BSTR_ERR_TOO_LARGE;
         }
         // the keys in the order their blocks entered the reference's map = the order of the reads that made them
-        std::vector<std::pair<int32_t, uint32_t>> made;
-        for (uint32_t k = 0; k < nkeys; k++) if (heads[k].created_by >= 0) made.push_back({heads[k].created_by, k});
-        std::sort(made.begin(), made.end());
-        std::vector<uint32_t> inserted(made.size());
-        for (size_t i = 0; i < made.size(); i++) inserted[i] = made[i].second;
+        // (a read makes at most one block)
+        std::vector<uint32_t> by_read(nreads, 0xFFFFFFFFu);
+        for (uint32_t k = 0; k < nkeys; k++) if (made[k] >= 0) by_read[(uint32_t)made[k]] = k;
+        std::vector<uint32_t> inserted;
+        inserted.reserve(nkeys);
+        for (uint32_t r = 0; r < nreads; r++) if (by_read[r] != 0xFFFFFFFFu) inserted.push_back(by_read[r]);
         st_blocks = inserted.size();
         const std::vector<uint32_t> listed = table_order(P.keys, inserted);
         std::vector<uint32_t> which;
-        for (uint32_t k : listed)
-            if (block_verdict(heads[k], (unsigned)min_threshold, (unsigned)max_threshold, include_all != 0).print) which.push_back(k);
+        for (uint32_t k : listed) if (printed[k]) which.push_back(k);
         st_printed = which.size();
         std::vector<char> oseq(which.size() * (size_t)MAXB), oqual(which.size() * (size_t)MAXB);
+        std::vector<BlockHead> heads(which.size());
         if (!which.empty()) {
             BM_UP(d_which, which.data(), which.size() * 4);
             BM_UP(d_oseq, (const void *)nullptr, oseq.size());
             BM_UP(d_oqual, (const void *)nullptr, oqual.size());
-            k_merge_gather<<<(unsigned)which.size(), 128, 0, st>>>(d_which.as<uint32_t>(), (uint32_t)which.size(), d_bseq.as<char>(), d_bqual.as<char>(),
-                                                                  d_oseq.as<char>(), d_oqual.as<char>());
+            BM_UP(d_ohead, (const void *)nullptr, which.size() * sizeof(BlockHead));
+            k_merge_gather<<<(unsigned)which.size(), 128, 0, st>>>(d_which.as<uint32_t>(), (uint32_t)which.size(), d_heads.as<BlockHead>(), d_bseq.as<char>(),
+                                                                  d_bqual.as<char>(), d_ohead.as<BlockHead>(), d_oseq.as<char>(), d_oqual.as<char>());
             CUDA_TRY(cudaGetLastError());
             CUDA_TRY(cudaMemcpyAsync(oseq.data(), d_oseq.p, oseq.size(), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaMemcpyAsync(oqual.data(), d_oqual.p, oqual.size(), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaMemcpyAsync(heads.data(), d_ohead.p, which.size() * sizeof(BlockHead), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaStreamSynchronize(st));
         }
 #undef BM_UP
         unsigned bindex = 1;
         for (size_t b = 0; b < which.size(); b++)
-            print_block(out, bindex, P.keys.key(which[b]), heads[which[b]], &oseq[b * (size_t)MAXB], &oqual[b * (size_t)MAXB], (unsigned)min_threshold,
+            print_block(out, bindex, P.keys.key(which[b]), heads[b], &oseq[b * (size_t)MAXB], &oqual[b * (size_t)MAXB], (unsigned)min_threshold,
                         (unsigned)max_threshold, include_all != 0);
         ms_dev = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
     }

@@ -175,4 +175,18 @@ BM_HD int create_block(BlockHead *h, char *bseq, char *bqual, const Read &r, con
     return ERR_NONE;
 }
 
+// what the reference would print of a block: the first (up to three) copy numbers with >= 2
+// supporting reads, newest entry of the list first (:445-455), and whether the block is printed (:457-460)
+struct Verdict { unsigned copies[3], maxcopies; bool print; };
+BM_HD Verdict block_verdict(const BlockHead &h, unsigned min_threshold, unsigned max_threshold, bool include_all)
+{
+    Verdict v = {{0, 0, 0}, 0, false};
+    int i = 0;
+    for (int s = (int)h.nsup - 1; s >= 0 && i < 3; s--)      // the reference's list has the newest entry first
+        if (h.sup_n[s] >= 2) { v.copies[i] = h.sup_copies[s]; if (v.copies[i] > v.maxcopies) v.maxcopies = v.copies[i]; i++; }
+    v.print = h.support >= min_threshold && h.support <= max_threshold &&
+              ((!include_all && v.copies[2] == 0 && v.copies[1] != 0) || (include_all && v.copies[2] == 0));
+    return v;
+}
+
 }  // namespace bmerge

@@ -15,10 +15,14 @@
 #pragma once
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
+#include <chrono>
+#include <functional>
+#include <memory>
 #include <string>
-#include <unordered_map>
+#include <thread>
 #include <vector>
 
 #include "merge_core.cuh"
@@ -52,10 +56,10 @@ struct KeyTable {
     std::vector<uint32_t> slot;                 // id + 1, 0 = empty
     uint64_t mask = 0;
     static uint64_t hash_of(const char *p, size_t n);
-    uint32_t intern(const char *p, size_t n)
+    uint32_t intern(const char *p, size_t n) { return intern(p, n, hash_of(p, n)); }
+    uint32_t intern(const char *p, size_t n, uint64_t h)
     {
         if ((start.size() + 1) * 2 > slot.size()) grow();
-        const uint64_t h = hash_of(p, n);
         for (uint64_t at = h & mask;; at = (at + 1) & mask) {
             const uint32_t id1 = slot[at];
             if (!id1) {
@@ -83,10 +87,30 @@ struct KeyTable {
     size_t size() const { return start.size(); }
 };
 
+struct Blob {                                    // bytes that are written before they are read: not cleared on allocation
+    std::unique_ptr<char[]> p;
+    size_t n = 0;
+    void resize(size_t bytes) { p.reset(new char[bytes ? bytes : 1]); n = bytes; }
+    char *data() { return p.get(); }
+    const char *data() const { return p.get(); }
+    size_t size() const { return n; }
+    char &operator[](size_t i) { return p[i]; }
+};
+
+// the distinct keys of the input: ids, hashes (for the table order) and texts (for the motif when printing)
+struct Keys {
+    std::vector<uint64_t> hash;                 // per key id
+    std::vector<const char *> text;             // into the shards' arenas
+    std::vector<uint32_t> len;
+    std::vector<KeyTable> shard;                // interned per hash range, by one thread each
+    size_t size() const { return hash.size(); }
+    std::string key(uint32_t id) const { return std::string(text[id], len[id]); }
+};
+
 struct Plan {
     std::vector<Read> reads;
-    std::string fwd, rev, qfwd, qrev;           // blobs: bases / qualities, as read and reversed(-complemented)
-    KeyTable keys;                              // key id -> "motif lflank rflank"
+    Blob fwd, rev, qfwd, qrev;                  // bases / qualities, as read and reversed(-complemented)
+    Keys keys;                                  // key id -> "motif lflank rflank"
     std::vector<uint32_t> chain_start;          // chains (components): reads of chain c = chain_reads[chain_start[c] .. chain_start[c+1])
     std::vector<uint32_t> chain_reads;          // in input order within a chain
     std::string error;
@@ -118,70 +142,170 @@ inline bool parse_name(const char *s, const char *e, Read &r)
 }
 
 // reads + blobs + key ids + chains; false (plan.error set) on input the reference would die on or
-// read out of bounds for
-inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P)
+// read out of bounds for.  Parsing, both strands and the key hashes run on `threads` host threads over
+// ranges of records; the keys are interned and the chains built by one
+inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P, unsigned threads = 0, bool host_strands = true)
 {
-    char msg[256];
-    const char *p = (const char *)raw, *end = p + nbytes;
-    uint64_t recno = 0;
-    P.fwd.reserve(nbytes / 2); P.qfwd.reserve(nbytes / 2); P.rev.reserve(nbytes / 2); P.qrev.reserve(nbytes / 2);
-    P.reads.reserve(nbytes / 256);
-    auto line = [&](const char *&s, const char *&e) {
-        if (p >= end) return false;
-        s = p;
-        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
-        e = nl ? nl : end;
-        p = nl ? nl + 1 : end;
-        return true;
+    const char *text = (const char *)raw;
+    const bool trace = getenv("BSTR_TRACE_PLAN") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto tp = now();
+    auto lap = [&](const char *what) { if (trace) { auto t = now(); fprintf(stderr, "[merge plan] %-28s %.1f ms\n", what, std::chrono::duration<double, std::milli>(t - tp).count()); tp = t; } };
+    if (threads == 0) { threads = std::thread::hardware_concurrency(); if (threads == 0) threads = 1; if (threads > 16) threads = 16; }
+    if (nbytes < (4u << 20)) threads = 1;
+    auto parallel = [&](size_t n, const std::function<void(unsigned, size_t, size_t)> &fn) {
+        if (threads <= 1 || n < threads) { fn(0, 0, n); return; }
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < threads; t++) pool.emplace_back(fn, t, n * t / threads, n * (t + 1) / threads);
+        for (auto &th : pool) th.join();
     };
-    for (;;) {
-        const char *ns, *ne, *bs, *be, *ps, *pe, *qs, *qe;
-        if (!line(ns, ne) || ns == ne) break;                                // end of input (fastq_seq.c:44-51)
-        recno++;
-        if (!line(bs, be) || !line(ps, pe) || !line(qs, qe) || *ns != '@' || ps == pe || *ps != '+') {
-            snprintf(msg, sizeof msg, "merge: record %llu is not a 4-line FASTQ record", (unsigned long long)recno);
-            P.error = msg; return false;
+    // 1. line ends
+    std::vector<std::vector<uint64_t>> part(threads);
+    parallel((size_t)nbytes, [&](unsigned t, size_t lo, size_t hi) {
+        std::vector<uint64_t> &v = part[t];
+        v.reserve((hi - lo) / 64 + 16);
+        for (const char *q = text + lo, *e = text + hi; q < e;) {
+            const char *nl = (const char *)memchr(q, '\n', (size_t)(e - q));
+            if (!nl) break;
+            v.push_back((uint64_t)(nl - text));
+            q = nl + 1;
         }
-        Read r;
-        memset(&r, 0, sizeof r);
-        if (!parse_name(ns, ne, r)) {
-            snprintf(msg, sizeof msg, "merge: error in parsing read name of record %llu (merge_STR_reads.c:350-355)", (unsigned long long)recno);
-            P.error = msg; return false;
+    });
+    std::vector<uint64_t> nl;
+    { size_t total = 1; for (auto &v : part) total += v.size(); nl.reserve(total); }
+    for (auto &v : part) nl.insert(nl.end(), v.begin(), v.end());
+    if (nbytes && text[nbytes - 1] != '\n') nl.push_back(nbytes);               // an unterminated last line
+    lap("line ends");
+    auto line_start = [&](size_t i) { return i ? nl[i - 1] + 1 : 0; };
+    size_t nrec = nl.size() / 4;
+    const bool ragged = nl.size() % 4 != 0;
+    // 2. names, lengths, checks; the input ends at the first record whose name line is empty (fastq_seq.c:44-51)
+    P.reads.assign(nrec, Read());
+    std::vector<uint64_t> stop(threads, UINT64_MAX), bad(threads, UINT64_MAX);
+    std::vector<int> why(threads, 0);
+    const int k = klength;
+    parallel(nrec, [&](unsigned t, size_t lo, size_t hi) {
+        for (size_t r = lo; r < hi; r++) {
+            const char *ns = text + line_start(4 * r), *ne = text + nl[4 * r], *bs = text + line_start(4 * r + 1), *be = text + nl[4 * r + 1],
+                       *ps = text + line_start(4 * r + 2), *pe = text + nl[4 * r + 2], *qs = text + line_start(4 * r + 3), *qe = text + nl[4 * r + 3];
+            if (ns == ne) { stop[t] = r; return; }
+            Read &rd = P.reads[r];
+            memset(&rd, 0, sizeof rd);
+            int e = 0;
+            const size_t L = (size_t)(be - bs);
+            if (*ns != '@' || ps == pe || *ps != '+') e = 1;
+            else if (!parse_name(ns, ne, rd)) e = 2;
+            else if ((size_t)(qe - qs) != L || L == 0 || L > 65535) e = 3;
+            else if (rd.fzstart < k || rd.fend + k > (int)L || rd.rzstart < k || rd.rend + k > (int)L || rd.fend < rd.fzstart || rd.rend < rd.rzstart) e = 4;
+            if (e) { bad[t] = r; why[t] = e; return; }
+            rd.slen = (uint16_t)L;
         }
-        const size_t L = (size_t)(be - bs);
-        if ((size_t)(qe - qs) != L || L == 0 || L > 65535) {
-            snprintf(msg, sizeof msg, "merge: record %llu: bases and qualities differ in length (or are empty)", (unsigned long long)recno);
-            P.error = msg; return false;
-        }
-        r.slen = (uint16_t)L;
-        r.off = (uint32_t)P.fwd.size();
-        if (P.fwd.size() + L + 1 > 0xFFFFFFF0ull) { P.error = "merge: more than 4 GiB of reads in one call"; return false; }
-        P.fwd.append(bs, L); P.fwd.push_back('\0');
-        P.qfwd.append(qs, L); P.qfwd.push_back('\0');
-        P.rev.resize(P.fwd.size()); P.qrev.resize(P.fwd.size());
-        {
-            const unsigned char *comp = complement_table();
-            char *rv = &P.rev[r.off], *qv = &P.qrev[r.off];
-            for (size_t i = 0; i < L; i++) { rv[i] = (char)comp[(unsigned char)bs[L - 1 - i]]; qv[i] = qs[L - 1 - i]; }
-            rv[L] = 0; qv[L] = 0;
-        }
-        const int k = klength;
-        if (r.fzstart < k || r.fend + k > (int)L || r.rzstart < k || r.rend + k > (int)L || r.fend < r.fzstart || r.rend < r.rzstart) {
-            snprintf(msg, sizeof msg, "merge: record %llu: a flank is shorter than klength %d (the reference reads outside the read there)", (unsigned long long)recno, k);
-            P.error = msg; return false;
-        }
-        char key[8 + 2 * 1000 + 4];
-        auto make_key = [&](const char *motif, int mlen, const char *bases, int zstart, int end_) {
-            char *q = key;
-            memcpy(q, motif, (size_t)mlen); q += mlen; *q++ = ' ';
-            memcpy(q, bases + zstart - k, (size_t)k); q += k; *q++ = ' ';
-            memcpy(q, bases + end_, (size_t)k); q += k;
-            return (size_t)(q - key);
-        };
-        r.fkey = P.keys.intern(key, make_key(r.fmotif, r.fmlen, P.fwd.data() + r.off, r.fzstart, r.fend));
-        r.rkey = P.keys.intern(key, make_key(r.rmotif, r.rmlen, P.rev.data() + r.off, r.rzstart, r.rend));
-        P.reads.push_back(r);
+    });
+    lap("names, lengths, checks");
+    uint64_t first_stop = UINT64_MAX, first_bad = UINT64_MAX;
+    int reason = 0;
+    for (unsigned t = 0; t < threads; t++) {
+        if (stop[t] < first_stop) first_stop = stop[t];
+        if (bad[t] < first_bad) { first_bad = bad[t]; reason = why[t]; }
     }
+    if (first_stop != UINT64_MAX) nrec = (size_t)first_stop;
+    else if (ragged && !(nl.size() % 4 == 1 && line_start(nl.size() - 1) == nl.back())) { first_bad = first_bad < nrec ? first_bad : nrec; if (first_bad == nrec) reason = 1; }
+    if (first_bad < nrec || (first_bad == nrec && reason == 1 && first_stop == UINT64_MAX)) {
+        char msg[256];
+        const unsigned long long recno = (unsigned long long)first_bad + 1;
+        if (reason == 1) snprintf(msg, sizeof msg, "merge: record %llu is not a 4-line FASTQ record", recno);
+        else if (reason == 2) snprintf(msg, sizeof msg, "merge: error in parsing read name of record %llu (merge_STR_reads.c:350-355)", recno);
+        else if (reason == 3) snprintf(msg, sizeof msg, "merge: record %llu: bases and qualities differ in length (or are empty)", recno);
+        else snprintf(msg, sizeof msg, "merge: record %llu: a flank is shorter than klength %d (the reference reads outside the read there)", recno, k);
+        P.error = msg;
+        return false;
+    }
+    P.reads.resize(nrec);
+    // 3. offsets of the reads in the blobs
+    uint64_t total = 0;
+    for (size_t r = 0; r < nrec; r++) { P.reads[r].off = (uint32_t)total; total += (uint64_t)P.reads[r].slen + 1; }
+    if (total > 0xFFFFFFF0ull) { P.error = "merge: more than 4 GiB of reads in one call"; return false; }
+    // host_strands = false: the caller reverses the reads itself (merge.cu does it on the device); only the
+    // two flanks of the reverse strand's key are complemented here
+    P.fwd.resize(total); P.qfwd.resize(total);
+    if (host_strands) { P.rev.resize(total); P.qrev.resize(total); }
+    lap("offsets, blob allocation");
+    // 4. both strands, and the two keys of every read with their hashes
+    struct KeyRef { uint64_t hash; uint32_t at, len; };
+    std::vector<KeyRef> kref(2 * nrec);
+    std::vector<std::string> arena(threads);
+    std::vector<unsigned> owner(nrec ? nrec : 1);
+    parallel(nrec, [&](unsigned t, size_t lo, size_t hi) {
+        const unsigned char *comp = complement_table();
+        std::string &ar = arena[t];
+        ar.reserve((hi - lo) * (size_t)(2 * (2 * k + 8)));
+        for (size_t r = lo; r < hi; r++) {
+            Read &rd = P.reads[r];
+            const size_t L = rd.slen;
+            const char *bs = text + line_start(4 * r + 1), *qs = text + line_start(4 * r + 3);
+            char *fw = &P.fwd[rd.off], *qf = &P.qfwd[rd.off];
+            memcpy(fw, bs, L); fw[L] = 0;
+            memcpy(qf, qs, L); qf[L] = 0;
+            if (host_strands) {
+                char *rv = &P.rev[rd.off], *qv = &P.qrev[rd.off];
+                for (size_t i = 0; i < L; i++) { rv[i] = (char)comp[(unsigned char)bs[L - 1 - i]]; qv[i] = qs[L - 1 - i]; }
+                rv[L] = 0; qv[L] = 0;
+            }
+            auto make_key = [&](const char *motif, int mlen, const char *bases, int zstart, int end_, KeyRef &out) {
+                out.at = (uint32_t)ar.size();
+                ar.append(motif, (size_t)mlen).push_back(' ');
+                ar.append(bases + zstart - k, (size_t)k).push_back(' ');
+                ar.append(bases + end_, (size_t)k);
+                out.len = (uint32_t)(ar.size() - out.at);
+                out.hash = KeyTable::hash_of(ar.data() + out.at, out.len);
+            };
+            make_key(rd.fmotif, rd.fmlen, fw, rd.fzstart, rd.fend, kref[2 * r]);
+            {   // the reverse strand's key: rev[i] = complement(fwd[L - 1 - i])
+                KeyRef &out = kref[2 * r + 1];
+                out.at = (uint32_t)ar.size();
+                ar.append(rd.rmotif, (size_t)rd.rmlen).push_back(' ');
+                for (int i = rd.rzstart - k; i < rd.rzstart; i++) ar.push_back((char)comp[(unsigned char)bs[L - 1 - i]]);
+                ar.push_back(' ');
+                for (int i = rd.rend; i < rd.rend + k; i++) ar.push_back((char)comp[(unsigned char)bs[L - 1 - i]]);
+                out.len = (uint32_t)(ar.size() - out.at);
+                out.hash = KeyTable::hash_of(ar.data() + out.at, out.len);
+            }
+            owner[r] = t;
+        }
+    });
+    lap("strands, keys, hashes");
+    // 5. key ids: the keys are split by hash over `threads` tables, every thread interns its share of all
+    // keys (no locks), then the tables' local ids are made global by their tables' offsets
+    P.keys.shard.assign(threads, KeyTable());
+    parallel(threads, [&](unsigned, size_t lo, size_t hi) {
+        for (size_t sh = lo; sh < hi; sh++) {
+            KeyTable &T = P.keys.shard[sh];
+            for (size_t i = 0; i < 2 * nrec; i++) {
+                const KeyRef &kr = kref[i];
+                if ((kr.hash >> 40) % threads != sh) continue;
+                const uint32_t id = T.intern(arena[owner[i >> 1]].data() + kr.at, kr.len, kr.hash);
+                if (i & 1) P.reads[i >> 1].rkey = id; else P.reads[i >> 1].fkey = id;
+            }
+        }
+    });
+    std::vector<uint32_t> base(threads + 1, 0);
+    for (unsigned sh = 0; sh < threads; sh++) base[sh + 1] = base[sh] + (uint32_t)P.keys.shard[sh].size();
+    P.keys.hash.resize(base[threads]); P.keys.text.resize(base[threads]); P.keys.len.resize(base[threads]);
+    parallel(threads, [&](unsigned, size_t lo, size_t hi) {
+        for (size_t sh = lo; sh < hi; sh++) {
+            const KeyTable &T = P.keys.shard[sh];
+            for (uint32_t id = 0; id < T.size(); id++) {
+                P.keys.hash[base[sh] + id] = T.hash[id]; P.keys.text[base[sh] + id] = T.arena.data() + T.start[id]; P.keys.len[base[sh] + id] = T.len[id];
+            }
+        }
+    });
+    parallel(nrec, [&](unsigned, size_t lo, size_t hi) {
+        for (size_t r = lo; r < hi; r++) {
+            P.reads[r].fkey += base[(kref[2 * r].hash >> 40) % threads];
+            P.reads[r].rkey += base[(kref[2 * r + 1].hash >> 40) % threads];
+        }
+    });
+    lap("key ids");
     // chains: union-find over key ids, a read joins its two keys
     std::vector<uint32_t> parent(P.keys.size());
     for (uint32_t i = 0; i < parent.size(); i++) parent[i] = i;
@@ -202,6 +326,7 @@ inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P)
     P.chain_reads.resize(P.reads.size());
     std::vector<uint32_t> fill(P.chain_start.begin(), P.chain_start.end() - 1);
     for (size_t i = 0; i < P.reads.size(); i++) P.chain_reads[fill[read_chain[i]]++] = (uint32_t)i;
+    lap("chains");
     return true;
 }
 
@@ -246,7 +371,7 @@ inline uint64_t murmur3_x64_128_low(const void *data, size_t len)
 // key ids in the order the reference's table would list them, given the order they were inserted in
 inline uint64_t KeyTable::hash_of(const char *p, size_t n) { return murmur3_x64_128_low(p, n); }
 
-inline std::vector<uint32_t> table_order(const KeyTable &keys, const std::vector<uint32_t> &inserted)
+inline std::vector<uint32_t> table_order(const Keys &keys, const std::vector<uint32_t> &inserted)
 {
     std::vector<uint64_t> hash(inserted.size());
     // the map's key type is a pointer (const char *): sparsehash drops the "known-0" low bits of the
@@ -281,20 +406,6 @@ inline std::vector<uint32_t> table_order(const KeyTable &keys, const std::vector
 }
 
 // ---------------------------------------------------------------- printing (:438-505)
-
-// what the reference would print of a block: the first (up to three) copy numbers with >= 2
-// supporting reads, newest entry of the list first (:445-455), and whether the block is printed (:457-460)
-struct Verdict { unsigned copies[3], maxcopies; bool print; };
-inline Verdict block_verdict(const BlockHead &h, unsigned min_threshold, unsigned max_threshold, bool include_all)
-{
-    Verdict v = {{0, 0, 0}, 0, false};
-    int i = 0;
-    for (int s = (int)h.nsup - 1; s >= 0 && i < 3; s--)      // the reference's list has the newest entry first
-        if (h.sup_n[s] >= 2) { v.copies[i] = h.sup_copies[s]; if (v.copies[i] > v.maxcopies) v.maxcopies = v.copies[i]; i++; }
-    v.print = h.support >= min_threshold && h.support <= max_threshold &&
-              ((!include_all && v.copies[2] == 0 && v.copies[1] != 0) || (include_all && v.copies[2] == 0));
-    return v;
-}
 
 // appends the block's four lines if it passes the thresholds; returns whether it did
 inline bool print_block(std::string &out, unsigned &bindex, const std::string &key, const BlockHead &h, const char *seq, const char *qual,
