@@ -33,11 +33,16 @@ inline bool make_plan(const uint8_t *raw, uint64_t nbytes, Plan &P)
         p = nl ? nl + 1 : end;
         return true;
     };
+    if (nbytes && raw[nbytes - 1] != '\n') {
+        // GetZippedLine returns -1 for a line that ends at the end of the file (utilities.c:205-207): the reference dies
+        P.error = "extend: the last line is not terminated by a newline (the reference's reader fails on it, utilities.c:205)";
+        return false;
+    }
     for (;;) {
         const char *ns, *ne, *bs, *be, *ps, *pe, *qs, *qe;
-        if (!line(ns, ne) || ns == ne) break;
+        if (!line(ns, ne)) break;                            // only the end of the text ends the input (fastq_seq.c:44-52)
         recno++;
-        if (!line(bs, be) || !line(ps, pe) || !line(qs, qe) || *ns != '@' || ps == pe || *ps != '+') {
+        if (ns == ne || !line(bs, be) || !line(ps, pe) || !line(qs, qe) || *ns != '@' || ps == pe || *ps != '+') {
             snprintf(msg, sizeof msg, "extend: block %llu is not a 4-line FASTQ record", (unsigned long long)recno);
             P.error = msg; return false;
         }

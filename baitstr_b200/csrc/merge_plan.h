@@ -174,26 +174,30 @@ inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P,
     std::vector<uint64_t> nl;
     { size_t total = 1; for (auto &v : part) total += v.size(); nl.reserve(total); }
     for (auto &v : part) nl.insert(nl.end(), v.begin(), v.end());
-    if (nbytes && text[nbytes - 1] != '\n') nl.push_back(nbytes);               // an unterminated last line
+    if (nbytes && text[nbytes - 1] != '\n') {
+        // GetZippedLine returns -1 for a line that ends at the end of the file (utilities.c:205-207): the reference dies
+        P.error = "merge: the last line is not terminated by a newline (the reference's reader fails on it, utilities.c:205)";
+        return false;
+    }
     lap("line ends");
     auto line_start = [&](size_t i) { return i ? nl[i - 1] + 1 : 0; };
     size_t nrec = nl.size() / 4;
     const bool ragged = nl.size() % 4 != 0;
-    // 2. names, lengths, checks; the input ends at the first record whose name line is empty (fastq_seq.c:44-51)
+    // 2. names, lengths, checks.  Only the end of the text ends the input: a blank line where a record should start
+    // fails the reference's assertion (fastq_seq.c:52)
     P.reads.assign(nrec, Read());
-    std::vector<uint64_t> stop(threads, UINT64_MAX), bad(threads, UINT64_MAX);
+    std::vector<uint64_t> bad(threads, UINT64_MAX);
     std::vector<int> why(threads, 0);
     const int k = klength;
     parallel(nrec, [&](unsigned t, size_t lo, size_t hi) {
         for (size_t r = lo; r < hi; r++) {
             const char *ns = text + line_start(4 * r), *ne = text + nl[4 * r], *bs = text + line_start(4 * r + 1), *be = text + nl[4 * r + 1],
                        *ps = text + line_start(4 * r + 2), *pe = text + nl[4 * r + 2], *qs = text + line_start(4 * r + 3), *qe = text + nl[4 * r + 3];
-            if (ns == ne) { stop[t] = r; return; }
             Read &rd = P.reads[r];
             memset(&rd, 0, sizeof rd);
             int e = 0;
             const size_t L = (size_t)(be - bs);
-            if (*ns != '@' || ps == pe || *ps != '+') e = 1;
+            if (ns == ne || *ns != '@' || ps == pe || *ps != '+') e = 1;
             else if (!parse_name(ns, ne, rd)) e = 2;
             else if ((size_t)(qe - qs) != L || L == 0 || L > 65535) e = 3;
             else if (rd.fzstart < k || rd.fend + k > (int)L || rd.rzstart < k || rd.rend + k > (int)L || rd.fend < rd.fzstart || rd.rend < rd.rzstart) e = 4;
@@ -202,15 +206,12 @@ inline bool make_plan(const uint8_t *raw, uint64_t nbytes, int klength, Plan &P,
         }
     });
     lap("names, lengths, checks");
-    uint64_t first_stop = UINT64_MAX, first_bad = UINT64_MAX;
+    uint64_t first_bad = UINT64_MAX;
     int reason = 0;
-    for (unsigned t = 0; t < threads; t++) {
-        if (stop[t] < first_stop) first_stop = stop[t];
+    for (unsigned t = 0; t < threads; t++)
         if (bad[t] < first_bad) { first_bad = bad[t]; reason = why[t]; }
-    }
-    if (first_stop != UINT64_MAX) nrec = (size_t)first_stop;
-    else if (ragged && !(nl.size() % 4 == 1 && line_start(nl.size() - 1) == nl.back())) { first_bad = first_bad < nrec ? first_bad : nrec; if (first_bad == nrec) reason = 1; }
-    if (first_bad < nrec || (first_bad == nrec && reason == 1 && first_stop == UINT64_MAX)) {
+    if (first_bad >= nrec && ragged) { first_bad = nrec; reason = 1; }          // lines behind the last whole record: half a record
+    if (first_bad <= nrec && first_bad != UINT64_MAX) {
         char msg[256];
         const unsigned long long recno = (unsigned long long)first_bad + 1;
         if (reason == 1) snprintf(msg, sizeof msg, "merge: record %llu is not a 4-line FASTQ record", recno);

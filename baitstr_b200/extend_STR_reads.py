@@ -40,9 +40,7 @@ def read_file(path):
         raw = f.read()
     if raw[:2] == b"\x1f\x8b":          # gzopen reads either (fastq_seq.c:9)
         raw = gzip.decompress(raw)
-    if raw and not raw.endswith(b"\n"):
-        raw += b"\n"
-    return raw
+    return raw          # an unterminated last line is an error below, as in the reference's reader (utilities.c:205)
 
 
 def record_chunks(raw, limit=CHUNK):

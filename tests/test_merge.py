@@ -116,6 +116,28 @@ def test_host_build_matches_the_reference_binary(case, tmp_path):
     assert blocks > 100
 
 
+def test_host_build_input_edges(tmp_path):
+    """only the end of the text ends the input: a blank line where a record should start fails the reference's assertion
+    (fastq_seq.c:52), an unterminated last line its reader (utilities.c:205), half a record its record checks -- all
+    are errors here too, with nothing printed"""
+    sel = util.gz_read("testdata_readme.out.gz")
+    cases = (("blank_line_at_the_end", sel + b"\n", "27", b"record 120 is not a 4-line FASTQ record"),
+             ("records_behind_a_blank_line", sel + b"\n@x\nACGT\n+\nIIII\n", "27", b"record 120 is not a 4-line FASTQ record"),
+             ("no_final_newline", sel[:-1], "27", b"last line is not terminated"),
+             ("half_a_record", sel + b"@x\nACGT\n", "27", b"record 120 is not a 4-line FASTQ record"),
+             ("cut_inside_a_record", b"\n".join(sel.split(b"\n")[:10]) + b"\n", "27", b"record 3 is not a 4-line FASTQ record"),
+             ("not_the_select_output", util.gz_read("testdata_1.fq.gz")[:4000].rsplit(b"\n@", 1)[0] + b"\n", "27", b"error in parsing read name of record 1"),
+             ("flank_shorter_than_klength", sel, "31", b"a flank is shorter than klength 31"))
+    for name, data, k, what in cases:
+        path = write(tmp_path, name + ".fq", data)
+        r = subprocess.run([emul_bin(), k, "2", "10000", "1", path], capture_output=True)
+        assert r.returncode != 0 and r.stdout == b"" and what in r.stderr, (name, r.stderr)
+        if os.path.exists(REF_BIN):                              # the reference does not survive these either
+            rr = subprocess.run([REF_BIN, "--all", "--min_threshold=2", k, path], capture_output=True)
+            assert rr.returncode != 0 and rr.stdout == b"", name
+    assert emulated(write(tmp_path, "empty.fq", b""), 27, 2, 10000, True) == b""
+
+
 def test_table_order_replay_is_exercised():
     """the order of the printed blocks is the reference's hash-table order: more blocks than the 32
     starting buckets, so the replay has grown and rehashed the table several times"""
