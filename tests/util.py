@@ -221,3 +221,52 @@ def diploid_str_reads(genome_len, nloci, coverage, L, seed, snp_every=250, err=0
         q = "".join(chr(rng.choice([40, 50, 53, 54, 60, 70, 73])) if rng.random() < 0.1 else "I" for _ in range(L))
         out.append("@d.%08d/1\n%s\n+\n%s\n" % (idx, s, q))
     return "".join(out).encode("latin-1")
+
+
+def diploid_str_reads_np(genome_len, nloci, coverage, L, seed, snp_every=250, err=0.004):
+    """diploid_str_reads for large inputs (numpy): the same kind of genome -- STR loci with different copy numbers
+    on the two haplotypes, a SNP about every `snp_every` bases -- and reads of both strands with substitution errors"""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    step = genome_len // (nloci + 1)
+    parts_a, parts_b = [], []
+    for locus in range(nloci + 1):
+        unique = rng.integers(0, 4, step, dtype=np.uint8)
+        other = unique.copy()
+        snp = rng.random(step) < 1.0 / snp_every
+        other[snp] = (other[snp] + rng.integers(1, 4, int(snp.sum()), dtype=np.uint8)) & 3
+        parts_a.append(unique)
+        parts_b.append(other)
+        if locus < nloci:
+            k = int(rng.integers(2, 7))
+            while True:
+                motif = rng.integers(0, 4, k, dtype=np.uint8)
+                if len(set(motif.tolist())) > 1:
+                    break
+            c = int(rng.integers(5, 13))
+            c2 = c if rng.random() < 0.3 else max(3, c + int(rng.choice([-2, -1, 1, 2, 3])))
+            parts_a.append(np.tile(motif, c))
+            parts_b.append(np.tile(motif, c2))
+    haps = [np.concatenate(parts_a), np.concatenate(parts_b)]
+    nreads = coverage * len(haps[0]) // L
+    half = nreads // 2
+    codes = np.empty((nreads, L), np.uint8)
+    for h, (lo, hi) in enumerate(((0, half), (half, nreads))):
+        starts = rng.integers(0, len(haps[h]) - L, hi - lo)
+        codes[lo:hi] = haps[h][starts[:, None] + np.arange(L)[None, :]]
+    rng.shuffle(codes, axis=0)
+    hit = rng.random(codes.shape) < err
+    codes[hit] = (codes[hit] + rng.integers(1, 4, int(hit.sum()), dtype=np.uint8)) & 3
+    flip = rng.random(nreads) < 0.5
+    codes[flip] = 3 - codes[flip][:, ::-1]
+    bases = np.frombuffer(b"ACGT", np.uint8)[codes]
+    quals = np.full((nreads, L), ord("I"), np.uint8)
+    low = rng.random(quals.shape) < 0.1
+    quals[low] = rng.choice(np.frombuffer(b"(25<FI", np.uint8), int(low.sum()))
+    rec = np.empty((nreads, 14 + L + 3 + L + 1), np.uint8)
+    rec[:, :14] = np.array([list(b"@d.%08d/1\n" % i) for i in range(nreads)], np.uint8)
+    rec[:, 14:14 + L] = bases
+    rec[:, 14 + L:14 + L + 3] = np.frombuffer(b"\n+\n", np.uint8)
+    rec[:, 17 + L:17 + 2 * L] = quals
+    rec[:, -1] = 10
+    return rec.tobytes()
