@@ -25,18 +25,32 @@
 
 namespace bmerge {
 
-constexpr int WARPS = 5;           // chains in flight per CTA: shared memory allows one CTA per SM
-
-struct WarpShared {
-    uint8_t T[T_BYTES];
-    int16_t diag[3][MAXF + 1];
-    char cons[4][MAXB];
-    char seq[2][MAXF + 1];         // the two flanks being aligned
+// Shared memory of one warp for a geometry (longest flank maxf, consensus room cap): the two-bit traceback
+// matrix, three anti-diagonals of scores, four consensus strings, the two flanks being aligned
+struct Geometry {
+    int maxf, pitch, cap;
+    uint32_t o_diag, o_cons, o_seq, warp_bytes;
+    int warps, ctas_per_sm;
 };
-static_assert(sizeof(WarpShared) * WARPS <= 227 * 1024, "shared memory of one CTA");
+static Geometry geometry_for(int maxf)
+{
+    auto up16 = [](uint32_t x) { return (x + 15u) & ~15u; };
+    Geometry g;
+    g.maxf = maxf < 31 ? 31 : (maxf > MAXF ? MAXF : maxf);
+    g.pitch = pitch_for(g.maxf);
+    g.cap = 2 * g.maxf + 64 > MAXB ? MAXB : (int)up16(2 * g.maxf + 64);
+    g.o_diag = (uint32_t)t_bytes_for(g.maxf);
+    g.o_cons = g.o_diag + up16(3u * (g.maxf + 1) * 2u);
+    g.o_seq = g.o_cons + 4u * (uint32_t)g.cap;
+    g.warp_bytes = g.o_seq + up16(2u * (g.maxf + 1));
+    const uint32_t sm = 227u * 1024u;
+    g.warps = (int)std::min<uint32_t>(8u, sm / g.warp_bytes);
+    g.ctas_per_sm = (int)std::max<uint32_t>(1u, std::min<uint32_t>(8u, sm / (g.warps * g.warp_bytes + 1024u)));
+    return g;
+}
 
 struct WarpExec {
-    int lane;
+    int lane, pitch;
     int16_t *d0, *d1, *d2;
     char *s1, *s2;
     // Align's matrix (:86-110) along anti-diagonals d = i + j: a cell needs (i, j-1) and (i-1, j) of
@@ -57,7 +71,7 @@ struct WarpExec {
                     unsigned code;
                     const int a = dp_cell(left, up, dg, s1[i - 1] == s2[j - 1], &code);
                     cur[i] = (int16_t)a;
-                    t_put(T, i, j, code);            // cells of one diagonal lie PITCH - 1 apart: never in the same byte, 25 words apart
+                    t_put(T, pitch, i, j, code);     // cells of one diagonal lie pitch - 1 apart: never in the same byte, an odd number of words apart
                     const uint64_t key = best_key(a, i, j);
                     best = key > best ? key : best;
                 }
@@ -76,27 +90,43 @@ struct WarpExec {
     __device__ __forceinline__ void sync() const { __syncwarp(); }
 };
 
-// a warp per chain, chains handed out by a ticket (longest first: the host sorts them)
-__global__ void __launch_bounds__(WARPS * 32)
-k_merge_chains(const Read *reads, const uint32_t *chain_start, const uint32_t *chain_reads, const uint32_t *chain_order, uint32_t nchains,
+// a warp per chain, chains handed out by a ticket (longest first: the host sorts them).  With a redo list the
+// geometry is a small one: a chain that outgrows it (or fails in any way) is put on the list and walked
+// again by a second launch with the largest geometry, which first takes the chain's blocks back (`reset`)
+__global__ void __launch_bounds__(256)
+k_merge_chains(const Read *reads, const uint32_t *chain_start, const uint32_t *chain_reads, const uint32_t *work, uint32_t nwork,
                BlockHead *heads, char *bseqs, char *bquals, const char *fwd, const char *qfwd, const char *rev, const char *qrev,
-               unsigned *ticket, int *err)
+               unsigned *ticket, int *err, uint32_t *redo_list, unsigned *redo_count, int reset, Geometry g)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    WarpShared *w = reinterpret_cast<WarpShared *>(smem) + (threadIdx.x >> 5);
-    WarpExec x{(int)(threadIdx.x & 31), w->diag[0], w->diag[1], w->diag[2], w->seq[0], w->seq[1]};
-    const Scratch s{w->T, w->cons[0], w->cons[1], w->cons[2], w->cons[3]};
+    uint8_t *w = smem + (size_t)(threadIdx.x >> 5) * g.warp_bytes;
+    int16_t *diag = reinterpret_cast<int16_t *>(w + g.o_diag);
+    char *cons = reinterpret_cast<char *>(w + g.o_cons), *seq = reinterpret_cast<char *>(w + g.o_seq);
+    WarpExec x{(int)(threadIdx.x & 31), g.pitch, diag, diag + (g.maxf + 1), diag + 2 * (g.maxf + 1), seq, seq + (g.maxf + 1)};
+    const Scratch s{w, cons, cons + g.cap, cons + 2 * g.cap, cons + 3 * g.cap, g.maxf, g.pitch, g.cap};
     for (;;) {
         unsigned t = 0;
         if (x.lane == 0) t = atomicAdd(ticket, 1u);
         t = __shfl_sync(0xFFFFFFFFu, t, 0);
-        if (t >= nchains) return;
-        const uint32_t c = chain_order[t];
+        if (t >= nwork) return;
+        const uint32_t c = work[t];
+        if (reset) {
+            if (x.lane == 0)
+                for (uint32_t at = chain_start[c]; at < chain_start[c + 1]; at++) {
+                    const Read &r = reads[chain_reads[at]];
+                    heads[r.fkey].created_by = -1; heads[r.rkey].created_by = -1;
+                }
+            __syncwarp();
+        }
         for (uint32_t at = chain_start[c]; at < chain_start[c + 1]; at++) {
             const uint32_t i = chain_reads[at];
             const int e = process_read(x, reads[i], (int)i, heads, bseqs, bquals, fwd, qfwd, rev, qrev, s);
-            if (e) {                                   // the whole call fails: remember the first reason
-                if (x.lane == 0 && atomicCAS(&err[0], 0, e) == 0) err[1] = (int)i;
+            if (e) {
+                if (redo_list) {                       // too big for this geometry (or an error the second launch will name)
+                    if (x.lane == 0) redo_list[atomicAdd(redo_count, 1u)] = c;
+                    break;
+                }
+                if (x.lane == 0 && atomicCAS(&err[0], 0, e) == 0) err[1] = (int)i;   // the whole call fails: remember the first reason
                 return;
             }
         }
@@ -195,7 +225,7 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
     if (!make_plan(fastq, nbytes, klength, P, 0, false)) { set_error(ctx, "bstr_merge_reads: %s", P.error.c_str()); return BSTR_ERR_PARAM; }
     const uint32_t nreads = (uint32_t)P.reads.size(), nkeys = (uint32_t)P.keys.size(), nchains = (uint32_t)P.chain_start.size() - 1;
     std::string out;
-    uint64_t st_blocks = 0, st_printed = 0, st_longest = 0;
+    uint64_t st_blocks = 0, st_printed = 0, st_longest = 0, st_redone = 0;
     double ms_plan = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), ms_dev = 0, ms_kernel = 0;
     if (nreads) {
         // longest chains first
@@ -228,21 +258,43 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
         BM_UP(d_heads, (const void *)nullptr, (size_t)nkeys * sizeof(BlockHead));
         BM_UP(d_bseq, (const void *)nullptr, (size_t)nkeys * MAXB);
         BM_UP(d_bqual, (const void *)nullptr, (size_t)nkeys * MAXB);
-        BM_UP(d_misc, (const void *)nullptr, 16);
-        CUDA_TRY(cudaMemsetAsync(d_misc.p, 0, 16, st));
+        BM_UP(d_misc, (const void *)nullptr, 32);                       // ticket, error code, error read, chains to redo, ticket of the second launch
+        CUDA_TRY(cudaMemsetAsync(d_misc.p, 0, 32, st));
         k_merge_init<<<(nkeys + 255) / 256, 256, 0, st>>>(d_heads.as<BlockHead>(), nkeys);
         k_merge_strands<<<(nreads + 7) / 8, 256, 0, st>>>(d_reads.as<Read>(), nreads, d_fwd.as<char>(), d_qfwd.as<char>(), d_rev.as<char>(), d_qrev.as<char>());
-        const size_t smem = sizeof(WarpShared) * WARPS;
-        CUDA_TRY(cudaFuncSetAttribute(k_merge_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // geometry: sized for the longest flank of the input with room to grow; chains that outgrow it are redone
+        int longest_flank = 0;
+        for (const Read &r : P.reads)
+            longest_flank = std::max(longest_flank, std::max(std::max((int)r.fzstart, (int)r.slen - (int)r.fend), std::max((int)r.rzstart, (int)r.slen - (int)r.rend)));
+        const char *force = getenv("BSTR_MERGE_MAXF");                  // tests: a first geometry that most chains outgrow
+        const Geometry small = geometry_for(force ? atoi(force) : longest_flank + longest_flank / 4 + 16), full = geometry_for(MAXF);
+        const bool two_pass = small.maxf < full.maxf;
+        DevBuf d_redo;
+        if (two_pass) BM_UP(d_redo, (const void *)nullptr, (size_t)nchains * 4);
+        CUDA_TRY(cudaFuncSetAttribute(k_merge_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(full.warps * full.warp_bytes > small.warps * small.warp_bytes
+                                                                                                            ? full.warps * full.warp_bytes : small.warps * small.warp_bytes)));
         cudaEvent_t e0, e1;
         CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
-        const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, ((uint64_t)nchains + WARPS - 1) / WARPS);
+        auto launch = [&](const Geometry &g, const uint32_t *work, uint32_t nwork, unsigned *ticket, uint32_t *redo, unsigned *redo_count, int reset) {
+            const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count * g.ctas_per_sm, ((uint64_t)nwork + g.warps - 1) / g.warps);
+            k_merge_chains<<<grid ? grid : 1, g.warps * 32, (size_t)g.warps * g.warp_bytes, st>>>(
+                d_reads.as<Read>(), d_cs.as<uint32_t>(), d_cr.as<uint32_t>(), work, nwork, d_heads.as<BlockHead>(), d_bseq.as<char>(), d_bqual.as<char>(),
+                d_fwd.as<char>(), d_qfwd.as<char>(), d_rev.as<char>(), d_qrev.as<char>(), ticket, d_misc.as<int>() + 1, redo, redo_count, reset, g);
+        };
         cudaEventRecord(e0, st);
-        k_merge_chains<<<grid, WARPS * 32, smem, st>>>(d_reads.as<Read>(), d_cs.as<uint32_t>(), d_cr.as<uint32_t>(), d_co.as<uint32_t>(), nchains,
-                                                        d_heads.as<BlockHead>(), d_bseq.as<char>(), d_bqual.as<char>(), d_fwd.as<char>(),
-                                                        d_qfwd.as<char>(), d_rev.as<char>(), d_qrev.as<char>(), d_misc.as<unsigned>(),
-                                                        d_misc.as<int>() + 1);
+        unsigned redone = 0;
+        if (!two_pass) {
+            launch(full, d_co.as<uint32_t>(), nchains, d_misc.as<unsigned>(), nullptr, nullptr, 0);
+        } else {
+            launch(small, d_co.as<uint32_t>(), nchains, d_misc.as<unsigned>(), d_redo.as<uint32_t>(), d_misc.as<unsigned>() + 3, 0);
+            if (cudaMemcpyAsync(&redone, d_misc.as<unsigned>() + 3, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+                cudaEventDestroy(e0); cudaEventDestroy(e1);
+                return cuda_fail(ctx, cudaGetLastError(), "k_merge_chains", __LINE__);
+            }
+            if (redone) launch(full, d_redo.as<uint32_t>(), redone, d_misc.as<unsigned>() + 4, nullptr, nullptr, 1);
+        }
         cudaEventRecord(e1, st);
+        st_redone = redone;
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return cuda_fail(ctx, le, "k_merge_chains", __LINE__); }
         k_merge_verdicts<<<(nkeys + 255) / 256, 256, 0, st>>>(d_heads.as<BlockHead>(), nkeys, (uint32_t)min_threshold, (uint32_t)max_threshold, include_all,
@@ -307,7 +359,8 @@ extern "C" int bstr_merge_reads(bstr_ctx *ctx, const uint8_t *fastq, uint64_t nb
     }
     if (stats) { stats[0] = nreads; stats[1] = nkeys; stats[2] = nchains; stats[3] = st_blocks; stats[4] = st_printed; stats[5] = st_longest; }
     if (getenv("BSTR_TRACE"))
-        fprintf(stderr, "[bstr_merge] %u reads, %u keys, %u chains (longest %llu), %llu blocks, %llu printed: plan %.1f ms, device part %.1f ms (kernel %.2f ms)\n",
-                nreads, nkeys, nchains, (unsigned long long)st_longest, (unsigned long long)st_blocks, (unsigned long long)st_printed, ms_plan, ms_dev, ms_kernel);
+        fprintf(stderr, "[bstr_merge] %u reads, %u keys, %u chains (longest %llu), %llu blocks, %llu printed: plan %.1f ms, device part %.1f ms (kernels %.2f ms, %llu chains redone with the largest geometry)\n",
+                nreads, nkeys, nchains, (unsigned long long)st_longest, (unsigned long long)st_blocks, (unsigned long long)st_printed, ms_plan, ms_dev, ms_kernel,
+                (unsigned long long)st_redone);
     return BSTR_OK;
 }

@@ -51,15 +51,15 @@ struct Read {                      // one record of the select stage's output, p
 // the traceback matrix holds B[i][j] only (0 diagonal, 1 up, 2 left): the scores the reference reads
 // back from A during the traceback follow from the moves (a diagonal move came from A - (+1 | -1), a
 // gap move from A + 3), so A is never stored
-BM_HD void t_put(uint8_t *T, int i, int j, unsigned v)
+BM_HD void t_put(uint8_t *T, int pitch, int i, int j, unsigned v)
 {
-    const int at = i * PITCH + j, sh = (at & 3) * 2;
+    const int at = i * pitch + j, sh = (at & 3) * 2;
     uint8_t &b = T[at >> 2];
     b = (uint8_t)((b & ~(3u << sh)) | (v << sh));
 }
-BM_HD unsigned t_get(const uint8_t *T, int i, int j)
+BM_HD unsigned t_get(const uint8_t *T, int pitch, int i, int j)
 {
-    const int at = i * PITCH + j;
+    const int at = i * pitch + j;
     return (T[at >> 2] >> ((at & 3) * 2)) & 3u;
 }
 
@@ -85,16 +85,23 @@ struct AlignOut {
     int err;
 };
 
-// the traceback of Align (:112-205) from the best cell; consensus into seq/qual (capacity MAXB)
+// A geometry smaller than the largest (MAXF, PITCH, MAXB) lets more warps share an SM's shared memory; a
+// chain that outgrows it is walked again with the largest one (merge.cu).  The row pitch is chosen so
+// that the cells of one anti-diagonal, pitch - 1 apart, fall into different shared-memory banks:
+// (pitch - 1) / 16 words, an odd number
+BM_HD int pitch_for(int maxf) { int p = maxf + 1; while ((p - 1) % 32 != 16) p++; return p; }
+BM_HD int t_bytes_for(int maxf) { return ((maxf + 1) * pitch_for(maxf) / 4 + 15) / 16 * 16; }
+
+// the traceback of Align (:112-205) from the best cell; consensus into seq/qual (capacity cap <= MAXB)
 BM_HD void align_trace(const char *t1, const char *q1, int len1, const char *t2, const char *q2, int len2,
-                       const uint8_t *T, uint64_t best, bool right_gapped, char *seq, char *qual, AlignOut *o)
+                       const uint8_t *T, int pitch, int cap, uint64_t best, bool right_gapped, char *seq, char *qual, AlignOut *o)
 {
     int sindx = 0, err = ERR_NONE;
     unsigned i = (unsigned)(best >> 16) & 0xFFFFu, j = (unsigned)best & 0xFFFFu;
     int max_score = (int)(best >> 32);
     int matches = 0, mismatches = 0;
     unsigned num_gaps = 0;
-#define BM_EMIT(c, q) do { if (sindx < MAXB - 1) { seq[sindx] = (c); qual[sindx] = (q); sindx++; } else err = ERR_BLOCK_TOO_LONG; } while (0)
+#define BM_EMIT(c, q) do { if (sindx < cap - 1) { seq[sindx] = (c); qual[sindx] = (q); sindx++; } else err = ERR_BLOCK_TOO_LONG; } while (0)
     if (right_gapped) {
         // as the reference: the overhang of the LONGER flank beyond the best cell's column j -- compared
         // with j also when it walks the first sequence (:128-133)
@@ -104,7 +111,7 @@ BM_HD void align_trace(const char *t1, const char *q1, int len1, const char *t2,
         num_gaps = (unsigned)(len2 - (int)j - 1);
     }
     while (max_score > 0 && i >= 1 && j >= 1) {
-        const unsigned b = t_get(T, (int)i, (int)j);
+        const unsigned b = t_get(T, pitch, (int)i, (int)j);
         if (b == 0) {
             if (q1[i - 1] > q2[j - 1]) BM_EMIT(t1[i - 1], q1[i - 1]); else BM_EMIT(t2[j - 1], q2[j - 1]);
             if (t1[i - 1] != t2[j - 1]) { mismatches++; max_score += 1; } else { matches++; max_score -= 1; }

@@ -18,8 +18,9 @@
 namespace bmerge {
 
 struct Scratch {                   // per executor
-    uint8_t *T;                    // T_BYTES
-    char *lseq, *lqual, *rseq, *rqual;   // MAXB each
+    uint8_t *T;                    // t_bytes_for(maxf)
+    char *lseq, *lqual, *rseq, *rqual;   // cap each
+    int maxf, pitch, cap;          // the geometry: longest flank, row pitch of T (pitch_for(maxf)), room for a consensus flank
 };
 
 // AlignFlanks (:215-306).  Returns 1 merged, 0 not, < 0 = -(ERR_*)
@@ -30,12 +31,12 @@ BM_X int try_merge(X &x, BlockHead *h, char *bseq, char *bqual, const char *base
     const int zb = h->zstart, eb = h->end, sb = h->slen;
     // the sequences to the left of the STR: block [0, zstart], read [0, zstart]
     int len1 = zb + 1, len2 = zstart + 1;
-    if (len1 - 1 > MAXF || len2 - 1 > MAXF || sb - eb > MAXF || slen - end > MAXF) return -ERR_FLANK_TOO_LONG;
+    if (len1 - 1 > s.maxf || len2 - 1 > s.maxf || sb - eb > s.maxf || slen - end > s.maxf) return -ERR_FLANK_TOO_LONG;
     uint64_t best = x.dp_fill(bseq, len1, bases, len2, s.T);
     int verdict = 0, ln = 0;
     if (x.leader()) {
         AlignOut o;
-        align_trace(bseq, bqual, len1, bases, quals, len2, s.T, best, false, s.lseq, s.lqual, &o);
+        align_trace(bseq, bqual, len1, bases, quals, len2, s.T, s.pitch, s.cap, best, false, s.lseq, s.lqual, &o);
         ln = o.n;
         verdict = o.err ? -o.err : (align_rejected(o) ? 0 : 1);
     }
@@ -46,7 +47,7 @@ BM_X int try_merge(X &x, BlockHead *h, char *bseq, char *bqual, const char *base
     best = x.dp_fill(bseq + eb, len1, bases + end, len2, s.T);
     if (x.leader()) {
         AlignOut o;
-        align_trace(bseq + eb, bqual + eb, len1, bases + end, quals + end, len2, s.T, best, true, s.rseq, s.rqual, &o);
+        align_trace(bseq + eb, bqual + eb, len1, bases + end, quals + end, len2, s.T, s.pitch, s.cap, best, true, s.rseq, s.rqual, &o);
         verdict = o.err ? -o.err : (align_rejected(o) ? 0 : 1);
         if (verdict == 1) {
             const int e = apply_merge(h, bseq, bqual, s.lseq, s.lqual, ln, s.rseq, s.rqual, o.n, motif, mlen, copies);

@@ -28,7 +28,7 @@ struct HostExec {
                 unsigned code;
                 const int a = dp_cell(cur[j - 1], prev[j], prev[j - 1], t1[i - 1] == t2[j - 1], &code);
                 cur[j] = a;
-                t_put(T, i, j, code);
+                t_put(T, PITCH, i, j, code);
                 const uint64_t key = best_key(a, i, j);
                 if (key > best) best = key;
             }
@@ -60,7 +60,7 @@ int main(int argc, char **argv)
     std::vector<char> bseqs(P.keys.size() * (size_t)MAXB), bquals(P.keys.size() * (size_t)MAXB);
     std::vector<uint8_t> T(T_BYTES);
     std::vector<char> sc(4 * MAXB);
-    Scratch s{T.data(), sc.data(), sc.data() + MAXB, sc.data() + 2 * MAXB, sc.data() + 3 * MAXB};
+    Scratch s{T.data(), sc.data(), sc.data() + MAXB, sc.data() + 2 * MAXB, sc.data() + 3 * MAXB, MAXF, PITCH, MAXB};
     HostExec x;
     // chain by chain, as the device does (the order of the chains does not matter)
     for (size_t c = 0; c + 1 < P.chain_start.size(); c++)

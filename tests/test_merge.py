@@ -178,6 +178,20 @@ def test_gpu_matches_the_reference_binary(capi, case, tmp_path):
 
 
 @pytest.mark.gpu
+def test_gpu_chains_that_outgrow_the_first_geometry_are_redone(capi, tmp_path, monkeypatch):
+    """the kernel first runs with shared memory sized for the input's longest flank; a chain that outgrows it is walked
+    again with the largest geometry.  Forced here (BSTR_MERGE_MAXF): flanks of up to 40 / 70 bases only in the first launch"""
+    sel = selected("150bp")
+    path = write(tmp_path, "reads.str.fq", sel)
+    want = reference(path, 27, 2, 10000, True) if os.path.exists(REF_BIN) else emulated(path, 27, 2, 10000, True)
+    for maxf in ("40", "70", "383"):
+        monkeypatch.setenv("BSTR_MERGE_MAXF", maxf)
+        with capi.Context() as ctx:
+            assert ctx.merge_reads(sel, 27, 2, 10000, True)[0] == want, maxf
+            assert ctx.merge_reads(util.gz_read("testdata_default.out.gz"), 27, 2, 10000, True)[0] == golden("merge_default_k27_all_min2.txt"), maxf
+
+
+@pytest.mark.gpu
 def test_gpu_select_then_merge_on_the_gpu(capi, tmp_path):
     """both stages on the GPU: this repository's select output fed to its merge stage equals the
     reference's merge of the same reads"""
