@@ -51,9 +51,11 @@ def record_chunks(raw, limit=CHUNK):
             yield raw[pos:]
             return
         lines = raw.count(b"\n", pos, pos + limit)
-        cut = pos
-        for _ in range(lines - lines % 4):
-            cut = raw.index(b"\n", cut) + 1
+        cut = raw.rfind(b"\n", pos, pos + limit) + 1           # behind the last newline of the window ...
+        for _ in range(lines % 4):                               # ... and back over the lines of the record it cuts
+            cut = raw.rfind(b"\n", pos, cut - 1) + 1
+        if lines < 4:
+            cut = pos
         if cut == pos:
             raise Die("a record longer than %d bytes" % limit)
         yield raw[pos:cut]
